@@ -1,0 +1,232 @@
+// C-ABI of libcacophony_b200.so (see include/cacophony_b200.h for the contract and the
+// reference callables each entry point replaces).  No CPU fallback: without a CUDA device
+// every compute entry point fails with CAC_ERR_NO_DEVICE / CAC_ERR_CUDA.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "cac_common.cuh"
+
+namespace cac {
+cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st);
+size_t feat_smem_bytes(const FeatArgs& a);
+cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st);
+cudaError_t launch_normalize(const float* in, float* out, long long rows, int row_len, cudaStream_t st);
+cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power, cudaStream_t st);
+cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, long long item_len, unsigned* work,
+                               cudaStream_t st);
+}  // namespace cac
+
+using namespace cac;
+
+static thread_local std::string g_err;
+static std::atomic<uint64_t> g_next_plan_id{1};
+static uint64_t g_const_owner[64] = {0};   // plan whose band table is in __constant__ memory, per device
+
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return fail(CAC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));     \
+    } while (0)
+
+struct cac_plan {
+    cac_params p;
+    int device;
+    int n_frames;
+    uint64_t id;
+    BandTable bt;
+    std::vector<float> weights;
+    int kmin, kmax;
+    int frames_per_stage, stage_half;
+    std::string fused_unsupported;   // why cac_features_run cannot serve these parameters ("" = it can)
+    // buffers owned by the *_host entry points
+    float* d_pcm = nullptr;      size_t pcm_cap = 0;
+    cac_segment* d_segs = nullptr; size_t segs_cap = 0;
+    float* d_out = nullptr;      size_t out_cap = 0;
+    void* d_work = nullptr;      size_t work_cap = 0;
+};
+
+extern "C" const char* cac_version(void) { return "cacophony_b200 0.1.0 (sm_100a)"; }
+extern "C" const char* cac_last_error(void) { return g_err.c_str(); }
+
+extern "C" int cac_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fail(CAC_ERR_NO_DEVICE, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    return n;
+}
+
+static int ensure_constants(cac_plan* plan, cudaStream_t st) {
+    if (plan->device < 64 && g_const_owner[plan->device] == plan->id) return CAC_OK;
+    CUDA_TRY(upload_bands(plan->bt, plan->weights.data(), (int)plan->weights.size(), st));
+    if (plan->device < 64) g_const_owner[plan->device] = plan->id;
+    return CAC_OK;
+}
+
+extern "C" int cac_plan_create(const cac_params* params, const float* w, int device, cac_plan** out) {
+    if (!params || !w || !out) return fail(CAC_ERR_INVALID, "null argument");
+    const cac_params& p = *params;
+    if (p.n_fft < 8 || (p.n_fft & 1)) return fail(CAC_ERR_INVALID, "n_fft must be even and >= 8");
+    if (p.hop_length < 1 || p.hop_length > p.n_fft) return fail(CAC_ERR_INVALID, "hop_length out of range");
+    if (p.n_mels < 1 || p.n_mels > kMaxMels) return fail(CAC_ERR_INVALID, "n_mels out of range");
+    if (p.power != 1 && p.power != 2) return fail(CAC_ERR_INVALID, "power must be 1 or 2");
+    if (p.segment_samples < 1) return fail(CAC_ERR_INVALID, "segment_samples must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+        return fail(CAC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU path)");
+    if (device < 0 || device >= ndev) return fail(CAC_ERR_INVALID, "device index out of range");
+
+    cac_plan* plan = new cac_plan();
+    plan->p = p;
+    plan->device = device;
+    plan->id = g_next_plan_id++;
+    plan->n_frames = 1 + p.segment_samples / p.hop_length;
+    const int bins = 1 + p.n_fft / 2;
+    int kmin = bins, kmax = -1;
+    for (int m = 0; m < p.n_mels; ++m) {
+        int first = -1, last = -1;
+        for (int k = 0; k < bins; ++k)
+            if (w[(size_t)m * bins + k] != 0.0f) { if (first < 0) first = k; last = k; }
+        if (first < 0) { first = 0; last = -1; }          // empty filter: contributes zero
+        plan->bt.start[m] = (int16_t)first;
+        plan->bt.len[m] = (int16_t)(last - first + 1);
+        plan->bt.off[m] = (int32_t)plan->weights.size();
+        for (int k = first; k <= last; ++k) plan->weights.push_back(w[(size_t)m * bins + k]);
+        if (last >= first) { kmin = first < kmin ? first : kmin; kmax = last > kmax ? last : kmax; }
+    }
+    if (kmax < 0) { kmin = 0; kmax = 0; }
+    for (int m = 0; m < p.n_mels; ++m)
+        if (plan->bt.len[m] == 0) plan->bt.start[m] = (int16_t)kmin;
+    if ((int)plan->weights.size() > kMaxTaps) { delete plan; return fail(CAC_ERR_INVALID, "filterbank has too many taps"); }
+    if (p.n_fft != 4096) plan->fused_unsupported = "fused STFT->mel kernel supports n_fft == 4096 only";
+    else if (kmax >= 1024) plan->fused_unsupported = "fused STFT->mel kernel covers FFT bins < 1024 (fmax < sr/4)";
+    plan->kmin = kmin;
+    plan->kmax = kmax;
+    // frames staged per round: largest multiple of 8 that fits the 227 KB shared-memory budget
+    plan->frames_per_stage = 0;
+    for (int fs = 32; fs >= 8; fs -= 8) {
+        int stage_len = (fs - 1) * p.hop_length + 4096;
+        int half = (((stage_len + 1) / 2 + 1 + 31) / 32) * 32 + 16;
+        FeatArgs a{};
+        a.stage_half = half;
+        a.nbins = kmax - kmin + 1;
+        if (feat_smem_bytes(a) <= 227 * 1024) { plan->frames_per_stage = fs; plan->stage_half = half; break; }
+    }
+    if (!plan->frames_per_stage && plan->fused_unsupported.empty())
+        plan->fused_unsupported = "parameters exceed the shared-memory budget of the fused kernel";
+    *out = plan;
+    return CAC_OK;
+}
+
+extern "C" int cac_plan_destroy(cac_plan* plan) {
+    if (!plan) return CAC_OK;
+    cudaSetDevice(plan->device);
+    cudaFree(plan->d_pcm); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
+    if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
+    delete plan;
+    return CAC_OK;
+}
+
+extern "C" int cac_plan_frames(const cac_plan* plan) { return plan ? plan->n_frames : CAC_ERR_INVALID; }
+
+extern "C" size_t cac_features_work_bytes(const cac_plan* plan, int64_t n) {
+    (void)plan;
+    return (size_t)(n > 0 ? n : 0) * (sizeof(float2) + sizeof(unsigned)) + 256;
+}
+
+extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_segment* d_segs, int64_t n,
+                                float* d_out, void* d_work, void* stream) {
+    if (!plan || !d_pcm || !d_segs || !d_out || !d_work) return fail(CAC_ERR_INVALID, "null argument");
+    if (!plan->fused_unsupported.empty()) return fail(CAC_ERR_INVALID, plan->fused_unsupported);
+    if (n == 0) return CAC_OK;
+    if (n < 0 || n * ((plan->n_frames + 31) / 32) > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_segments out of range");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    int rc = ensure_constants(plan, st);
+    if (rc) return rc;
+    FeatArgs a{};
+    a.pcm = d_pcm; a.segs = d_segs; a.out = d_out;
+    a.segstat = (float2*)d_work;
+    a.segmax = (unsigned*)((char*)d_work + (((size_t)n * sizeof(float2) + 127) / 128) * 128);
+    a.n_segs = n;
+    a.seg_len = plan->p.segment_samples;
+    a.hop = plan->p.hop_length;
+    a.n_frames = plan->n_frames;
+    a.n_mels = plan->p.n_mels;
+    a.kmin = plan->kmin;
+    a.nbins = plan->kmax - plan->kmin + 1;
+    a.tiles_per_seg = (plan->n_frames + 31) / 32;
+    a.frames_per_stage = plan->frames_per_stage;
+    a.stage_half = plan->stage_half;
+    a.normalize = plan->p.normalize;
+    CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st));
+    return CAC_OK;
+}
+
+template <class T>
+static int ensure_cap(T** ptr, size_t* cap, size_t bytes) {
+    if (bytes <= *cap) return CAC_OK;
+    if (*ptr) cudaFree(*ptr);
+    *ptr = nullptr; *cap = 0;
+    cudaError_t e = cudaMalloc((void**)ptr, bytes);
+    if (e != cudaSuccess) return fail(CAC_ERR_ALLOC, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    *cap = bytes;
+    return CAC_OK;
+}
+
+extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segs,
+                                 int64_t n, float* h_out) {
+    if (!plan || !h_pcm || !h_segs || !h_out) return fail(CAC_ERR_INVALID, "null argument");
+    if (n <= 0) return CAC_OK;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    for (int64_t i = 0; i < n; ++i) {
+        const cac_segment& s = h_segs[i];
+        if (s.n_valid < 0 || s.pad_left < 0 || s.pad_left + (int64_t)s.n_valid > plan->p.segment_samples ||
+            s.pcm_offset < 0 || s.pcm_offset + s.n_valid > n_pcm)
+            return fail(CAC_ERR_INVALID, "segment descriptor out of bounds");
+    }
+    const size_t out_bytes = (size_t)n * plan->p.n_mels * plan->n_frames * sizeof(float);
+    int rc;
+    if ((rc = ensure_cap(&plan->d_pcm, &plan->pcm_cap, (size_t)n_pcm * sizeof(float) + 16))) return rc;
+    if ((rc = ensure_cap(&plan->d_segs, &plan->segs_cap, (size_t)n * sizeof(cac_segment)))) return rc;
+    if ((rc = ensure_cap(&plan->d_out, &plan->out_cap, out_bytes))) return rc;
+    if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, cac_features_work_bytes(plan, n)))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(plan->d_pcm, h_pcm, (size_t)n_pcm * sizeof(float), cudaMemcpyHostToDevice, 0));
+    CUDA_TRY(cudaMemcpyAsync(plan->d_segs, h_segs, (size_t)n * sizeof(cac_segment), cudaMemcpyHostToDevice, 0));
+    if ((rc = cac_features_run(plan, plan->d_pcm, plan->d_segs, n, plan->d_out, plan->d_work, nullptr))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_out, plan->d_out, out_bytes, cudaMemcpyDeviceToHost, 0));
+    CUDA_TRY(cudaStreamSynchronize(0));
+    return CAC_OK;
+}
+
+extern "C" int cac_normalize_run(const float* d_in, float* d_out, int64_t n_rows, int32_t row_len, void* stream) {
+    if (!d_in || !d_out || n_rows < 0 || row_len < 1) return fail(CAC_ERR_INVALID, "bad argument");
+    if (n_rows == 0) return CAC_OK;
+    CUDA_TRY(launch_normalize(d_in, d_out, n_rows, row_len, (cudaStream_t)stream));
+    return CAC_OK;
+}
+
+extern "C" int cac_mel_project_run(cac_plan* plan, const float* d_mag, int32_t n_frames, float* d_out, void* stream) {
+    if (!plan || !d_mag || !d_out || n_frames < 0) return fail(CAC_ERR_INVALID, "bad argument");
+    if (n_frames == 0) return CAC_OK;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    int rc = ensure_constants(plan, (cudaStream_t)stream);
+    if (rc) return rc;
+    CUDA_TRY(launch_mel_project(d_mag, d_out, n_frames, plan->p.n_mels, plan->p.power, (cudaStream_t)stream));
+    return CAC_OK;
+}
+
+extern "C" int cac_power_to_db_run(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* d_work,
+                                   void* stream) {
+    if (!d_in || !d_out || !d_work || n_items < 0 || item_len < 1) return fail(CAC_ERR_INVALID, "bad argument");
+    if (n_items == 0) return CAC_OK;
+    CUDA_TRY(launch_power_to_db(d_in, d_out, n_items, item_len, (unsigned*)d_work, (cudaStream_t)stream));
+    return CAC_OK;
+}

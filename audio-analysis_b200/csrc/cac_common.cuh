@@ -1,0 +1,60 @@
+// Shared declarations for the cacophony_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/cacophony_b200.h"
+
+namespace cac {
+
+constexpr int kWarp = 32;
+constexpr int kMaxMels = 512;
+constexpr int kMaxTaps = 12288;   // packed band weights kept in __constant__ memory
+
+// Banded filterbank (one contiguous band per mel row), uploaded per plan.
+struct BandTable {
+    int16_t start[kMaxMels];   // first FFT bin of the band
+    int16_t len[kMaxMels];     // taps
+    int32_t off[kMaxMels];     // offset into weights[]
+};
+
+struct FeatArgs {
+    const float* pcm;
+    const cac_segment* segs;
+    float* out;            // [n_segs][n_mels][n_frames]
+    float2* segstat;       // [n_segs] (min, max) of the padded segment
+    unsigned* segmax;      // [n_segs] max mel value (float bits, values >= 0)
+    long long n_segs;
+    int seg_len;
+    int hop;
+    int n_frames;
+    int n_mels;
+    int kmin;              // lowest FFT bin any band touches
+    int nbins;             // kmax - kmin + 1
+    int tiles_per_seg;     // ceil(n_frames / 32)
+    int frames_per_stage;  // multiple of 8
+    int stage_half;        // floats reserved for each of the even/odd sample planes
+    int normalize;
+};
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// normalize_data (src/identify_tracks.py:202-209), same float32 op order:
+// x - min; / max(x - min); + 1e-6; - 0.5; * 2
+__device__ __forceinline__ float normalize_sample(float v, float mn, float range) {
+    float x = __fsub_rn(v, mn);
+    x = __fdiv_rn(x, range);
+    x = __fadd_rn(x, 0.000001f);
+    x = __fsub_rn(x, 0.5f);
+    return __fmul_rn(x, 2.0f);
+}
+
+}  // namespace cac

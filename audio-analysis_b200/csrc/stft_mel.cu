@@ -1,0 +1,393 @@
+// Fused framed real-FFT -> power -> banded mel projection for classifier segments.
+//
+// Replaces, for every segment of load_samples' loop (src/identify_tracks.py:163-190):
+//   normalize_data (:202-209) -> librosa.stft(n_fft=4096, hop) (:243) -> |.|**power
+//   (src/custommel.py:61) -> mel_f(...).dot(magnitude) (src/custommel.py:62-63)
+// The [2049 x frames] spectrum never leaves the SM: one warp transforms one frame
+// (4096 real points = 2048-point complex FFT as radix-64 x radix-32 in registers with a
+// single shared-memory transpose), the power spectrum of a 32-frame tile is parked in
+// shared memory and the sparse triangular filterbank is applied as banded dot products
+// with lanes = frames (conflict-free, weights broadcast from constant memory).
+#include "cac_common.cuh"
+#include "fft_regs.cuh"
+
+namespace cac {
+
+__constant__ BandTable c_bands;
+__constant__ float c_weights[kMaxTaps];
+
+constexpr int kNfft = 4096;
+constexpr int kExStride = 33;                 // floats per exchange row (odd -> conflict-free transpose)
+constexpr int kExFloats = 64 * kExStride;     // one plane (re or im) of one warp's exchange buffer
+constexpr int kWarpsPerCta = 8;
+constexpr int kTileFrames = 32;
+
+// ---- pass 1 input: 64 complex points z[32*i + lane] = (x[2n], x[2n+1]) * Hann ------------
+// Hann(s) = 0.5 - 0.5 cos(2 pi s / 4096) with s = 64*i + (2*lane + e): the cosine of the sum is
+// expanded so that the i-part is a compile-time constant and the lane part sits in 4 registers.
+template <int I>
+struct WinLoad {
+    static __device__ __forceinline__ void run(float (&re)[64], float (&im)[64], const float* pe,
+                                               const float* po, float hcb0, float hsb0, float hcb1,
+                                               float hsb1) {
+        constexpr float ca = (float)cx_cos2pi(I, 64);
+        constexpr float sa = (float)cx_sin2pi(I, 64);
+        float w0 = fmaf(-ca, hcb0, fmaf(sa, hsb0, 0.5f));
+        float w1 = fmaf(-ca, hcb1, fmaf(sa, hsb1, 0.5f));
+        re[I] = pe[32 * I] * w0;
+        im[I] = po[32 * I] * w1;
+        if constexpr (I + 1 < 64) WinLoad<I + 1>::run(re, im, pe, po, hcb0, hsb0, hcb1, hsb1);
+    }
+};
+
+// ---- transpose through shared memory: row k1 (pass-1 output index), column n2 (= lane) -----
+template <int K1>
+struct ExWrite {
+    static __device__ __forceinline__ void run(const float (&v)[64], float* ex_lane) {
+        ex_lane[K1 * kExStride] = v[out_pos(64, K1)];
+        if constexpr (K1 + 1 < 64) ExWrite<K1 + 1>::run(v, ex_lane);
+    }
+};
+template <int N2>
+struct ExRead {
+    static __device__ __forceinline__ void run(float (&v0)[32], float (&v1)[32], const float* ex_row) {
+        v0[N2] = ex_row[N2];
+        v1[N2] = ex_row[32 * kExStride + N2];
+        if constexpr (N2 + 1 < 32) ExRead<N2 + 1>::run(v0, v1, ex_row);
+    }
+};
+
+// ---- pass 2 twiddles: W2048^(k1*n2), k1 = lane + 32*H  ==  Tw_lane[n2] * W64^(H*n2) ----------
+template <int N2, int H>
+struct Pass2Tw {
+    static __device__ __forceinline__ void run(float (&re)[32], float (&im)[32], const float (&twr)[32],
+                                               const float (&twi)[32]) {
+        if constexpr (N2 > 0) {
+            float ar = re[N2], ai = im[N2];
+            if constexpr (H == 1) mul_twiddle<N2, 64>(ar, ai);
+            re[N2] = fmaf(-ai, twi[N2], ar * twr[N2]);
+            im[N2] = fmaf(ar, twi[N2], ai * twr[N2]);
+        }
+        if constexpr (N2 + 1 < 32) Pass2Tw<N2 + 1, H>::run(re, im, twr, twi);
+    }
+};
+
+// ---- real-FFT untangle + power, bins k = lane + 32*H + 64*K2 ---------------------------------
+// X[k] = (Z[k] + conj Z[2048-k])/2 - (i/2) W4096^k (Z[k] - conj Z[2048-k]); Z[2048-k] lives in
+// lane (32-lane)&31 (other half, index 31-K2), fetched with one shuffle per component.
+template <int K2, int H, int K2N, int POWER>
+struct Untangle {
+    static __device__ __forceinline__ void run(const float (&z0r)[32], const float (&z0i)[32],
+                                               const float (&z1r)[32], const float (&z1i)[32], int lane,
+                                               int partner, float bc, float bs, float* ptile, int fcol,
+                                               int kmin, int nbins) {
+        constexpr int pown = out_pos(32, K2);
+        constexpr int psend = out_pos(32, 31 - K2);
+        constexpr int psend0 = out_pos(32, (32 - K2) & 31);
+        float ar = H ? z1r[pown] : z0r[pown];
+        float ai = H ? z1i[pown] : z0i[pown];
+        // value this lane sends: the opposite half (lane 0 is its own partner and stays in its half)
+        float sr, si;
+        if constexpr (H == 0) {
+            sr = (lane == 0) ? z0r[psend0] : z1r[psend];
+            si = (lane == 0) ? z0i[psend0] : z1i[psend];
+        } else {
+            sr = (lane == 0) ? z1r[psend] : z0r[psend];
+            si = (lane == 0) ? z1i[psend] : z0i[psend];
+        }
+        float br = __shfl_sync(0xffffffffu, sr, partner);
+        float bi = -__shfl_sync(0xffffffffu, si, partner);   // conj
+        float sumr = ar + br, sumi = ai + bi;
+        float dr = ar - br, di = ai - bi;
+        mul_twiddle<K2, 64>(dr, di);                         // W4096^(64*K2)
+        float tr = fmaf(di, bs, dr * bc);                    // * W4096^(lane + 32H) = (bc, -bs)
+        float ti = fmaf(-dr, bs, di * bc);
+        float xr = 0.5f * (sumr + ti);
+        float xi = 0.5f * (sumi - tr);
+        float p = fmaf(xr, xr, xi * xi);
+        if constexpr (POWER == 1) p = sqrtf(p);
+        int kk = lane + 32 * H + 64 * K2 - kmin;
+        if (kk >= 0 && kk < nbins) ptile[kk * kTileFrames + ((fcol + kk) & 31)] = p;
+        if constexpr (K2 + 1 < K2N)
+            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, ptile, fcol, kmin,
+                                                 nbins);
+    }
+};
+
+struct LaneConsts {
+    float hcb0, hsb0, hcb1, hsb1;   // 0.5*cos / 0.5*sin of 2 pi (2 lane + e)/4096
+    float bc0, bs0, bc1, bs1;       // cos / sin of 2 pi (lane + 32 h)/4096
+};
+
+// One warp: Hann-windowed 4096-point real FFT of the frame starting at staged sample u0,
+// power spectrum of bins [kmin, kmin+nbins) written to column fcol of the tile.
+template <int POWER>
+__device__ __forceinline__ void fft_frame(const float* __restrict__ se, const float* __restrict__ so, int u0,
+                                          float* __restrict__ ex, float* __restrict__ ptile, int fcol, int lane,
+                                          const LaneConsts& lc, const float (&twr)[32], const float (&twi)[32],
+                                          int kmin, int nbins) {
+    float ar[64], ai[64];
+    {
+        const float* pe;
+        const float* po;
+        if (u0 & 1) { pe = so + (u0 >> 1) + lane; po = se + ((u0 + 1) >> 1) + lane; }
+        else        { pe = se + (u0 >> 1) + lane; po = so + (u0 >> 1) + lane; }
+        WinLoad<0>::run(ar, ai, pe, po, lc.hcb0, lc.hsb0, lc.hcb1, lc.hsb1);
+    }
+    fft_dif<64>(ar, ai);
+
+    float z0r[32], z0i[32], z1r[32], z1i[32];
+    __syncwarp();
+    ExWrite<0>::run(ar, ex + lane);
+    __syncwarp();
+    ExRead<0>::run(z0r, z1r, ex + lane * kExStride);
+    __syncwarp();
+    ExWrite<0>::run(ai, ex + lane);
+    __syncwarp();
+    ExRead<0>::run(z0i, z1i, ex + lane * kExStride);
+
+    Pass2Tw<0, 0>::run(z0r, z0i, twr, twi);
+    fft_dif<32>(z0r, z0i);
+    Pass2Tw<0, 1>::run(z1r, z1i, twr, twi);
+    fft_dif<32>(z1r, z1i);
+
+    const int partner = (32 - lane) & 31;
+    Untangle<0, 0, 16, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lc.bc0, lc.bs0, ptile, fcol, kmin, nbins);
+    Untangle<0, 1, 16, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lc.bc1, lc.bs1, ptile, fcol, kmin, nbins);
+}
+
+template <int POWER>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    float* se = smem;                              // even staged samples
+    float* so = se + a.stage_half;                 // odd staged samples
+    float* exbase = so + a.stage_half;             // 8 x kExFloats
+    float* ptile = exbase + kWarpsPerCta * kExFloats;   // nbins x 32
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long seg = blockIdx.x / a.tiles_per_seg;
+    const int tile = blockIdx.x - (int)(seg * a.tiles_per_seg);
+    const int f0 = tile * kTileFrames;
+    const int tf = min(kTileFrames, a.n_frames - f0);
+
+    const cac_segment sd = a.segs[seg];
+    float mn = 0.f, range = 1.f;
+    if (a.normalize) {
+        float2 st = a.segstat[seg];
+        mn = st.x;
+        range = __fsub_rn(st.y, st.x);
+    }
+
+    LaneConsts lc;
+    {
+        float s, c;
+        sincospif((float)(2 * lane) / 2048.0f, &s, &c);      lc.hcb0 = 0.5f * c; lc.hsb0 = 0.5f * s;
+        sincospif((float)(2 * lane + 1) / 2048.0f, &s, &c);  lc.hcb1 = 0.5f * c; lc.hsb1 = 0.5f * s;
+        sincospif((float)lane / 2048.0f, &s, &c);            lc.bc0 = c; lc.bs0 = s;
+        sincospif((float)(lane + 32) / 2048.0f, &s, &c);     lc.bc1 = c; lc.bs1 = s;
+    }
+    float twr[32], twi[32];
+#pragma unroll
+    for (int n2 = 0; n2 < 32; ++n2) {
+        float s, c;
+        sincospif((float)(lane * n2) / 1024.0f, &s, &c);     // exp(-2 pi i lane n2 / 2048)
+        twr[n2] = c;
+        twi[n2] = -s;
+    }
+
+    float* ex = exbase + warp * kExFloats;
+    for (int fs0 = 0; fs0 < tf; fs0 += a.frames_per_stage) {
+        const int nfs = min(a.frames_per_stage, tf - fs0);
+        const int p0 = (f0 + fs0) * a.hop;                    // padded-signal coordinate of stage start
+        const int len = (nfs - 1) * a.hop + kNfft;
+        __syncthreads();
+        for (int u = tid; u < len; u += kWarpsPerCta * 32) {
+            int s = p0 + u - kNfft / 2;                       // sample index inside the segment
+            float v = 0.f;
+            if (s >= 0 && s < a.seg_len) {
+                int r = s - sd.pad_left;
+                if (r >= 0 && r < sd.n_valid) v = __ldg(a.pcm + sd.pcm_offset + r);
+                if (a.normalize) v = normalize_sample(v, mn, range);
+            }
+            ((u & 1) ? so : se)[u >> 1] = v;
+        }
+        __syncthreads();
+        for (int fi = warp; fi < nfs; fi += kWarpsPerCta)
+            fft_frame<POWER>(se, so, fi * a.hop, ex, ptile, fs0 + fi, lane, lc, twr, twi, a.kmin, a.nbins);
+    }
+    __syncthreads();
+
+    // banded mel projection: lane = frame of the tile, warp w owns mel rows w, w+8, ...
+    float vmax = 0.f;
+    float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
+    for (int m = warp; m < a.n_mels; m += kWarpsPerCta) {
+        const int kk0 = c_bands.start[m] - a.kmin;
+        const int len = c_bands.len[m];
+        const float* w = c_weights + c_bands.off[m];
+        float acc = 0.f;
+        for (int t = 0; t < len; ++t) {
+            int kk = kk0 + t;
+            acc = fmaf(w[t], ptile[kk * kTileFrames + ((lane + kk) & 31)], acc);
+        }
+        if (lane < tf) {
+            outseg[(size_t)m * a.n_frames + f0 + lane] = acc;
+            vmax = fmaxf(vmax, acc);
+        }
+    }
+    vmax = warp_max(vmax);
+    if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
+}
+
+// ---- per-segment min / max of the zero-padded segment (normalize_data's reductions) ---------
+__global__ void __launch_bounds__(256) seg_minmax_kernel(const float* __restrict__ pcm,
+                                                         const cac_segment* __restrict__ segs,
+                                                         float2* __restrict__ segstat, unsigned* segmax,
+                                                         int seg_len) {
+    __shared__ float smn[8], smx[8];
+    const long long seg = blockIdx.x;
+    const cac_segment sd = segs[seg];
+    const float* p = pcm + sd.pcm_offset;
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = threadIdx.x; i < sd.n_valid; i += 256) {
+        float v = __ldg(p + i);
+        mn = fminf(mn, v);
+        mx = fmaxf(mx, v);
+    }
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+        if (sd.n_valid < seg_len) { mn = fminf(mn, 0.f); mx = fmaxf(mx, 0.f); }   // the np.pad zeros
+        segstat[seg] = make_float2(mn, mx);
+        segmax[seg] = 0u;
+    }
+}
+
+// ---- librosa.power_to_db(S, ref=np.max), top_db = 80, per item ------------------------------
+__global__ void __launch_bounds__(256) power_to_db_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                          const unsigned* __restrict__ itemmax,
+                                                          long long item_len, long long total) {
+    const float amin = 1e-10f;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        long long item = i / item_len;
+        float ref = __uint_as_float(itemmax[item]);
+        float refdb = 10.0f * log10f(fmaxf(amin, ref));
+        float v = 10.0f * log10f(fmaxf(amin, in[i]));
+        v = v - refdb;
+        // log_spec.max() is exactly 0 when ref is the block maximum, so the clamp floor is -top_db
+        float top = 10.0f * log10f(fmaxf(amin, ref)) - refdb;
+        out[i] = fmaxf(v, top - 80.0f);
+    }
+}
+
+__global__ void __launch_bounds__(256) item_max_kernel(const float* __restrict__ in, unsigned* itemmax,
+                                                       long long item_len) {
+    __shared__ float smx[8];
+    const float* p = in + (long long)blockIdx.x * item_len;
+    float mx = -INFINITY;
+    for (long long i = threadIdx.x; i < item_len; i += 256) mx = fmaxf(mx, p[i]);
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) smx[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) mx = fmaxf(mx, smx[w]);
+        itemmax[blockIdx.x] = __float_as_uint(mx);
+    }
+}
+
+// ---- normalize_data on independent rows ------------------------------------------------------
+__global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                             int row_len) {
+    __shared__ float smn[8], smx[8];
+    __shared__ float s_mn, s_range;
+    const float* p = in + (long long)blockIdx.x * row_len;
+    float* q = out + (long long)blockIdx.x * row_len;
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = threadIdx.x; i < row_len; i += 256) { float v = p[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
+    mn = warp_min(mn); mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+        s_mn = mn; s_range = __fsub_rn(mx, mn);
+    }
+    __syncthreads();
+    mn = s_mn; const float range = s_range;
+    for (int i = threadIdx.x; i < row_len; i += 256) q[i] = normalize_sample(p[i], mn, range);
+}
+
+// ---- custommel.mel_spec on a caller-supplied magnitude matrix [bins, frames] ----------------
+__global__ void __launch_bounds__(256) mel_project_kernel(const float* __restrict__ mag, float* __restrict__ out,
+                                                          int n_frames, int n_mels, int power) {
+    const int f = blockIdx.x * 256 + threadIdx.x;
+    const int m = blockIdx.y;
+    if (f >= n_frames) return;
+    const int k0 = c_bands.start[m], len = c_bands.len[m];
+    const float* w = c_weights + c_bands.off[m];
+    float acc = 0.f;
+    for (int t = 0; t < len; ++t) {
+        float v = fabsf(mag[(size_t)(k0 + t) * n_frames + f]);
+        if (power == 2) v = v * v;
+        else if (power != 1) v = powf(v, (float)power);
+        acc = fmaf(w[t], v, acc);
+    }
+    out[(size_t)m * n_frames + f] = acc;
+}
+
+}  // namespace cac
+
+// host-side launchers (called from cac_api.cu)
+namespace cac {
+
+cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st) {
+    cudaError_t e = cudaMemcpyToSymbolAsync(c_bands, &bt, sizeof(BandTable), 0, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbolAsync(c_weights, weights, sizeof(float) * n_taps, 0, cudaMemcpyHostToDevice, st);
+}
+
+size_t feat_smem_bytes(const FeatArgs& a) {
+    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kTileFrames);
+}
+
+cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st) {
+    seg_minmax_kernel<<<(unsigned)a.n_segs, 256, 0, st>>>(a.pcm, a.segs, a.segstat, a.segmax, a.seg_len);
+    const size_t smem = feat_smem_bytes(a);
+    auto kern = (power == 1) ? stft_mel_kernel<1> : stft_mel_kernel<2>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const long long grid = a.n_segs * a.tiles_per_seg;
+    kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, st>>>(a);
+    if (db_scale) {
+        const long long item = (long long)a.n_mels * a.n_frames, total = item * a.n_segs;
+        long long blocks = (total + 256 * 8 - 1) / (256 * 8);
+        if (blocks > 148LL * 64) blocks = 148LL * 64;
+        power_to_db_kernel<<<(unsigned)blocks, 256, 0, st>>>(a.out, a.out, a.segmax, item, total);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_normalize(const float* in, float* out, long long rows, int row_len, cudaStream_t st) {
+    normalize_rows_kernel<<<(unsigned)rows, 256, 0, st>>>(in, out, row_len);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power, cudaStream_t st) {
+    dim3 grid((n_frames + 255) / 256, n_mels);
+    mel_project_kernel<<<grid, 256, 0, st>>>(mag, out, n_frames, n_mels, power);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, long long item_len, unsigned* work,
+                               cudaStream_t st) {
+    item_max_kernel<<<(unsigned)n_items, 256, 0, st>>>(in, work, item_len);
+    const long long total = n_items * item_len;
+    long long blocks = (total + 256 * 8 - 1) / (256 * 8);
+    if (blocks > 148LL * 64) blocks = 148LL * 64;
+    if (blocks < 1) blocks = 1;
+    power_to_db_kernel<<<(unsigned)blocks, 256, 0, st>>>(in, out, work, item_len, total);
+    return cudaGetLastError();
+}
+
+}  // namespace cac

@@ -1,0 +1,178 @@
+"""ctypes binding of libcacophony_b200.so (include/cacophony_b200.h).
+
+PyTorch is used only for device memory and streams (tensors' data_ptr() are handed to the
+C-ABI).  There is no CPU fallback: a missing library raises ImportError here, and every
+compute call raises CacError when no CUDA device is present.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcacophony_b200.so")
+
+if not os.path.isfile(LIB_PATH):
+    raise ImportError(
+        "libcacophony_b200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'` "
+        "or audio-analysis_b200/csrc/build.sh); there is no CPU fallback")
+
+lib = ctypes.CDLL(LIB_PATH)
+
+
+class CacParams(ctypes.Structure):
+    _fields_ = [("sample_rate", ctypes.c_int32), ("n_fft", ctypes.c_int32), ("hop_length", ctypes.c_int32),
+                ("n_mels", ctypes.c_int32), ("segment_samples", ctypes.c_int32), ("power", ctypes.c_int32),
+                ("db_scale", ctypes.c_int32), ("normalize", ctypes.c_int32)]
+
+
+class CacSegment(ctypes.Structure):
+    _fields_ = [("pcm_offset", ctypes.c_int64), ("n_valid", ctypes.c_int32), ("pad_left", ctypes.c_int32)]
+
+
+SEGMENT_DTYPE = np.dtype([("pcm_offset", "<i8"), ("n_valid", "<i4"), ("pad_left", "<i4")])
+assert SEGMENT_DTYPE.itemsize == ctypes.sizeof(CacSegment) == 16
+
+_vp, _i64, _i32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32
+lib.cac_version.restype = ctypes.c_char_p
+lib.cac_last_error.restype = ctypes.c_char_p
+lib.cac_device_count.restype = ctypes.c_int
+lib.cac_plan_create.argtypes = [ctypes.POINTER(CacParams), _vp, ctypes.c_int, ctypes.POINTER(_vp)]
+lib.cac_plan_destroy.argtypes = [_vp]
+lib.cac_plan_frames.argtypes = [_vp]
+lib.cac_features_work_bytes.argtypes = [_vp, _i64]
+lib.cac_features_work_bytes.restype = ctypes.c_size_t
+lib.cac_features_run.argtypes = [_vp, _vp, _vp, _i64, _vp, _vp, _vp]
+lib.cac_features_host.argtypes = [_vp, _vp, _i64, _vp, _i64, _vp]
+lib.cac_normalize_run.argtypes = [_vp, _vp, _i64, _i32, _vp]
+lib.cac_mel_project_run.argtypes = [_vp, _vp, _i32, _vp, _vp]
+lib.cac_power_to_db_run.argtypes = [_vp, _vp, _i64, _i64, _vp, _vp]
+
+EXPORTS = ["cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
+           "cac_plan_frames", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
+           "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
+
+
+class CacError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise CacError("cacophony_b200 error %d: %s" % (rc, lib.cac_last_error().decode()))
+
+
+def version():
+    return lib.cac_version().decode()
+
+
+def _torch():
+    import torch
+    if not torch.cuda.is_available():
+        raise CacError("no CUDA device: cacophony_b200 has no CPU path")
+    return torch
+
+
+def _stream_ptr(torch):
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class FeaturePlan:
+    """STFT -> custom mel -> dB plan (cac_plan_*) for one DSP parameter set."""
+
+    def __init__(self, mel_weights, sr, n_fft, hop_length, n_mels, segment_samples, power=2, db_scale=True,
+                 normalize=True, device=0):
+        w = np.ascontiguousarray(mel_weights, dtype=np.float32)
+        assert w.shape == (n_mels, 1 + n_fft // 2), w.shape
+        self.params = CacParams(int(sr), int(n_fft), int(hop_length), int(n_mels), int(segment_samples),
+                                int(power), int(bool(db_scale)), int(bool(normalize)))
+        self.device = device
+        self._h = ctypes.c_void_p()
+        check(lib.cac_plan_create(ctypes.byref(self.params), w.ctypes.data_as(_vp), device, ctypes.byref(self._h)))
+        self.n_frames = lib.cac_plan_frames(self._h)
+        self.n_mels = int(n_mels)
+        self._work = None
+
+    def close(self):
+        if self._h:
+            lib.cac_plan_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- device-resident path -----------------------------------------------------------
+    def run(self, pcm, segments, out=None):
+        """pcm: float32 CUDA tensor (flat); segments: CUDA uint8/int tensor holding cac_segment
+        records (or a numpy SEGMENT_DTYPE array, uploaded here); returns [n, n_mels, frames]."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        if isinstance(segments, np.ndarray):
+            assert segments.dtype == SEGMENT_DTYPE
+            n = segments.shape[0]
+            segments = torch.from_numpy(segments.view(np.uint8).reshape(-1)).to(dev)
+        else:
+            n = segments.numel() * segments.element_size() // 16
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        if out is None:
+            out = torch.empty((n, self.n_mels, self.n_frames), dtype=torch.float32, device=dev)
+        need = lib.cac_features_work_bytes(self._h, n)
+        if self._work is None or self._work.numel() < need:
+            self._work = torch.empty(need, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_features_run(self._h, pcm.data_ptr(), segments.data_ptr(), n, out.data_ptr(),
+                                       self._work.data_ptr(), _stream_ptr(torch)))
+        return out
+
+    # ---- host-buffer path (H2D + run + D2H inside the call) ----------------------------------
+    def run_host(self, pcm, segments, out=None):
+        pcm = np.ascontiguousarray(pcm, dtype=np.float32).reshape(-1)
+        segments = np.ascontiguousarray(segments, dtype=SEGMENT_DTYPE)
+        n = segments.shape[0]
+        if out is None:
+            out = np.empty((n, self.n_mels, self.n_frames), dtype=np.float32)
+        check(lib.cac_features_host(self._h, pcm.ctypes.data_as(_vp), pcm.size, segments.ctypes.data_as(_vp), n,
+                                    out.ctypes.data_as(_vp)))
+        return out
+
+    def mel_project(self, mag):
+        """custommel.mel_spec on a magnitude matrix [bins, frames] (numpy or CUDA tensor)."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        was_np = isinstance(mag, np.ndarray)
+        t = torch.as_tensor(np.ascontiguousarray(mag, dtype=np.float32) if was_np else mag).to(dev).contiguous()
+        out = torch.empty((self.n_mels, t.shape[1]), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_mel_project_run(self._h, t.data_ptr(), t.shape[1], out.data_ptr(), _stream_ptr(torch)))
+        return out.cpu().numpy() if was_np else out
+
+
+def normalize_rows(x, device=0):
+    """normalize_data on the last axis (bit-exact float32 op order)."""
+    torch = _torch()
+    dev = torch.device("cuda", device)
+    was_np = isinstance(x, np.ndarray)
+    t = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32) if was_np else x).to(dev).contiguous()
+    out = torch.empty_like(t)
+    rows = t.numel() // t.shape[-1]
+    with torch.cuda.device(dev):
+        check(lib.cac_normalize_run(t.data_ptr(), out.data_ptr(), rows, t.shape[-1], _stream_ptr(torch)))
+    return out.cpu().numpy() if was_np else out
+
+
+def power_to_db(x, device=0):
+    """librosa.power_to_db(ref=np.max, top_db=80) per leading-axis item."""
+    torch = _torch()
+    dev = torch.device("cuda", device)
+    was_np = isinstance(x, np.ndarray)
+    t = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32) if was_np else x).to(dev).contiguous()
+    n_items = t.shape[0] if t.dim() > 2 else 1
+    out = torch.empty_like(t)
+    work = torch.empty(n_items * 4 + 16, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.cac_power_to_db_run(t.data_ptr(), out.data_ptr(), n_items, t.numel() // n_items, work.data_ptr(),
+                                      _stream_ptr(torch)))
+    return out.cpu().numpy() if was_np else out

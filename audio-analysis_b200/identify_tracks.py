@@ -1,0 +1,137 @@
+"""Drop-in for the feature-extraction half of the reference's identify_tracks module:
+load_samples / normalize_data / get_spect (src/identify_tracks.py:65-288) with the same
+signatures.  The slicing arithmetic (including the legacy global-RNG draws) runs on the
+host and produces a segment descriptor table; every sample-touching step (normalise, STFT,
+mel, dB) runs in the CUDA kernels behind engine.FeaturePlan.
+"""
+import functools
+import logging
+
+import numpy as np
+
+from . import custommel
+
+
+class Signal:
+    """Track record with the attributes load_samples reads (src/identify_tracks.py:915-986)."""
+
+    def __init__(self, start, end, freq_start, freq_end):
+        self.start = start
+        self.end = end
+        self.freq_start = freq_start
+        self.freq_end = freq_end
+
+    @property
+    def length(self):
+        return self.end - self.start
+
+
+@functools.lru_cache(maxsize=16)
+def _plan(sr, n_fft, hop_length, n_mels, fmin, fmax, mel_break, segment_samples, power, db_scale, normalize):
+    from . import engine
+    w = custommel._mel_f_cached(sr, n_mels, fmin, fmax, n_fft, mel_break)
+    return engine.FeaturePlan(w, sr, n_fft, hop_length, n_mels, segment_samples, power=power,
+                              db_scale=db_scale, normalize=normalize)
+
+
+def segment_descriptors(n_samples, sr, tracks, segment_length, stride, fmin=50, fmax=11000,
+                        pad_short_tracks=False, randint=None):
+    """Host half of load_samples (src/identify_tracks.py:109-196): returns
+    (descriptors[engine.SEGMENT_DTYPE], counts_per_track).  Consumes np.random.randint in the
+    same order as the reference (:132 once per short track, :167 once per short segment)."""
+    from .engine import SEGMENT_DTYPE
+    draw = randint or np.random.randint
+    seg_n = int(sr * segment_length)
+    rows, counts = [], []
+    for t in tracks:
+        if t.freq_start > fmax or t.freq_end < fmin:
+            counts.append(0)                      # placeholder track, nothing to classify
+            continue
+        lo, hi = int(sr * t.start), int(t.end * sr)
+        if not pad_short_tracks:
+            short_by = seg_n - (hi - lo)
+            if short_by > 0:                      # widen to exactly one segment around the track
+                shift = draw(0, short_by)
+                lo -= shift
+                if lo <= 0:
+                    lo, hi = 0, min(seg_n, n_samples)
+                else:
+                    hi = hi + short_by - shift
+                    if hi > n_samples:
+                        hi = n_samples
+                        lo = max(hi - seg_n, 0)
+                assert hi - lo == seg_n
+        base = min(max(lo, 0), n_samples)         # numpy slice clipping of frames[lo:hi]
+        avail = min(max(hi, base), n_samples) - base
+        a, b = 0, min(hi, seg_n)                  # first window ends at the ABSOLUTE index hi (:150-151)
+        t_start = 0
+        n_here = 0
+        while True:
+            a_c = min(a, avail)
+            n_valid = min(max(b, a_c), avail) - a_c
+            pad_left = int(draw(0, seg_n - n_valid)) if n_valid != seg_n else 0
+            rows.append((base + a_c, n_valid, pad_left))
+            n_here += 1
+            t_start = t_start + stride
+            t_end = t_start + segment_length
+            a = int(t_start * sr)
+            b = min(int(t_end * sr), a + seg_n)
+            if t_end > t.length:
+                break
+        counts.append(n_here)
+    return np.array(rows, dtype=SEGMENT_DTYPE).reshape(-1), counts
+
+
+def _finish(block, mean_sub, channels):
+    """get_spect tail (src/identify_tracks.py:267,282-287) on [n, n_mels, frames]."""
+    block = block[..., None]
+    if mean_sub:
+        block = block - np.mean(block, axis=2, keepdims=True, dtype=block.dtype)
+    if channels > 1:
+        block = np.repeat(block, channels, axis=3)
+    return block
+
+
+def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mean_sub=False, use_mfcc=False,
+                 mel_break=1000, htk=True, n_mels=160, fmin=50, fmax=11000, channels=1, power=2,
+                 db_scale=False, filter_freqs=False, filter_below=None, normalize=True, n_fft=4096,
+                 pad_short_tracks=False):
+    """Same signature and return structure as src/identify_tracks.py:65-199: one list per
+    track (empty for out-of-band tracks), each holding [n_mels, frames, channels] arrays."""
+    logging.debug("Loading samples with length %s stride %s hop length %s", segment_length, stride, hop_length)
+    if use_mfcc or not htk:
+        raise NotImplementedError("use_mfcc / htk=False branches (librosa.feature) are not built")
+    if filter_freqs or filter_below:
+        raise NotImplementedError("Butterworth pre-filter is a host pre-step outside this path")
+    frames = np.ascontiguousarray(frames, dtype=np.float32)
+    segs, counts = segment_descriptors(len(frames), sr, tracks, segment_length, stride, fmin, fmax,
+                                       pad_short_tracks)
+    if len(segs) == 0:
+        return [[] for _ in counts]
+    plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break,
+                 int(sr * segment_length), int(power), bool(db_scale), bool(normalize))
+    block = _finish(plan.run_host(frames, segs), mean_sub, channels)
+    out, k = [], 0
+    for c in counts:
+        out.append([block[k + i] for i in range(c)])
+        k += c
+    return out
+
+
+def normalize_data(x):
+    """src/identify_tracks.py:202-209 on the GPU (bit-exact float32 op order)."""
+    from . import engine
+    return engine.normalize_rows(np.asarray(x, dtype=np.float32))
+
+
+def get_spect(data, sr, hop_length, mean_sub, use_mfcc, mel_break, htk, n_mels, fmin, fmax, n_fft, power,
+              db_scale, channels=1, pass_freqs=None):
+    """src/identify_tracks.py:212-288 for one already-normalised segment."""
+    from .engine import SEGMENT_DTYPE
+    if use_mfcc or not htk:
+        raise NotImplementedError("use_mfcc / htk=False branches (librosa.feature) are not built")
+    data = np.ascontiguousarray(data, dtype=np.float32)
+    plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), 50 if fmin is None else fmin,
+                 11000 if fmin is None else fmax, mel_break, len(data), int(power), bool(db_scale), False)
+    seg = np.array([(0, len(data), 0)], dtype=SEGMENT_DTYPE)
+    return _finish(plan.run_host(data, seg), mean_sub, channels)[0]

@@ -1,0 +1,100 @@
+/* cacophony_b200 - C-ABI of the B200-native feature hot path of
+ * TheCacophonyProject/audio-analysis.
+ *
+ * The reference is pure Python and has no FFI/plugin boundary of its own:
+ * the seam is a set of Python callables.  Each entry point below names the reference
+ * callable (paths relative to /root/reference) whose arithmetic it replaces; the Python
+ * mirror of those callables lives in audio-analysis_b200/ and binds this header with
+ * ctypes (INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions: every function returns 0 on success or a negative cac_status; the message
+ * for the calling thread's last failure is cac_last_error().  Pointers named d_* are device
+ * pointers owned by the caller (e.g. torch tensors' data_ptr()), h_* are host pointers.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream).  *_run functions do
+ * not allocate or synchronise; *_host functions copy in, run, copy out and synchronise.
+ * There is no CPU fallback anywhere behind this interface.
+ */
+#ifndef CACOPHONY_B200_H
+#define CACOPHONY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum cac_status {
+    CAC_OK = 0,
+    CAC_ERR_INVALID = -1,     /* bad argument / unsupported parameter combination */
+    CAC_ERR_CUDA = -2,        /* a CUDA runtime call failed (message has the detail) */
+    CAC_ERR_NO_DEVICE = -3,   /* no CUDA device: this library never computes on the CPU */
+    CAC_ERR_ALLOC = -4
+} cac_status;
+
+/* DSP parameters of one classifier model: the keys of the model's metadata.txt read in
+ * identify_tracks.classify (src/identify_tracks.py:466-497) and passed to load_samples
+ * (src/identify_tracks.py:65-86). */
+typedef struct cac_params {
+    int32_t sample_rate;     /* sr, 48000 after load_recording (src/identify_tracks.py:49-57) */
+    int32_t n_fft;           /* 4096 (src/identify_tracks.py:85) */
+    int32_t hop_length;      /* 281 default of load_samples (:71); 640 classify fallback (:474) */
+    int32_t n_mels;          /* 160 */
+    int32_t segment_samples; /* int(sr * segment_length) (:109) */
+    int32_t power;           /* 1 or 2: exponent on |STFT| (src/custommel.py:61) */
+    int32_t db_scale;        /* librosa.power_to_db(ref=np.max) (src/identify_tracks.py:265-266) */
+    int32_t normalize;       /* normalize_data (src/identify_tracks.py:202-209) */
+} cac_params;
+
+/* One classifier segment = one get_spect call of the reference's segment loop
+ * (src/identify_tracks.py:163-196).  The segment's `segment_samples` samples are
+ * pad_left zeros, then n_valid samples pcm[pcm_offset ...], then zeros (np.pad at :165-168). */
+typedef struct cac_segment {
+    int64_t pcm_offset;
+    int32_t n_valid;
+    int32_t pad_left;
+} cac_segment;
+
+typedef struct cac_plan cac_plan;
+
+const char* cac_version(void);
+const char* cac_last_error(void);
+/* Number of visible CUDA devices (0 or negative status if none). */
+int cac_device_count(void);
+
+/* Plan for the STFT -> custom mel -> dB chain of get_spect (src/identify_tracks.py:212-288,
+ * htk=True branch) = librosa.stft (:243) + custommel.mel_spec (src/custommel.py:59-63) +
+ * librosa.power_to_db (:266).  `mel_weights` is the dense float32 [n_mels, 1+n_fft/2]
+ * filterbank exactly as custommel.mel_f returns it (src/custommel.py:19-56); rows must be
+ * contiguous bands (they are, for triangular filters).  The plan is bound to `device`. */
+int cac_plan_create(const cac_params* params, const float* h_mel_weights, int device, cac_plan** out);
+int cac_plan_destroy(cac_plan* plan);
+/* Frames per segment = 1 + segment_samples / hop_length (librosa.stft, center=True). */
+int cac_plan_frames(const cac_plan* plan);
+/* Bytes of device scratch cac_features_run needs for n_segments. */
+size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
+
+/* load_samples' inner loop (src/identify_tracks.py:163-190) for n_segments segments at once:
+ * d_out[s][m][f] float32 [n_segments, n_mels, frames] = get_spect(normalize_data(segment s)). */
+int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_segment* d_segments,
+                     int64_t n_segments, float* d_out, void* d_work, void* stream);
+/* Same through host buffers (H2D of pcm + descriptors, run, D2H of the result, synchronise). */
+int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segments,
+                      int64_t n_segments, float* h_out);
+
+/* normalize_data (src/identify_tracks.py:202-209) on n_rows rows of row_len samples (bit-exact op order). */
+int cac_normalize_run(const float* d_in, float* d_out, int64_t n_rows, int32_t row_len, void* stream);
+
+/* custommel.mel_spec (src/custommel.py:59-63): d_out[n_mels, n_frames] = W . |stft|**power, with
+ * d_mag the magnitude matrix [1+n_fft/2, n_frames] row-major (what np.abs(librosa.stft) returns). */
+int cac_mel_project_run(cac_plan* plan, const float* d_mag, int32_t n_frames, float* d_out, void* stream);
+
+/* librosa.power_to_db(S, ref=np.max) with top_db=80 on n_items independent blocks of item_len values
+ * (in place allowed). */
+int cac_power_to_db_run(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* d_work,
+                        void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CACOPHONY_B200_H */

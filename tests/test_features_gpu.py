@@ -1,0 +1,160 @@
+"""GPU parity: STFT -> custom mel -> dB through the C-ABI vs the oracle (same seeded inputs).
+Tolerances are BASELINE.json's: mel power <= 1e-4 relative, power_to_db <= 1e-2 dB max-abs,
+>= 90 % of outputs matching; slicing bit-exact."""
+import numpy as np
+import pytest
+
+from audio_analysis_b200 import synth
+from oracle import oracle_np as O
+
+pytestmark = pytest.mark.gpu
+
+S1 = dict(hop_length=281, mel_break=1750, n_mels=160, fmin=50, fmax=11000, power=2, n_fft=4096)
+
+
+def _match_fraction(got, ref, rtol):
+    return float(np.mean(np.abs(got - ref) <= rtol * np.abs(ref)))
+
+
+def test_library_loaded(engine):
+    assert "sm_100a" in engine.version()
+    assert engine.lib.cac_device_count() >= 1
+
+
+def test_normalize_bit_exact(engine):
+    from audio_analysis_b200 import identify_tracks as T
+    x = synth.recording(3, seconds=3.0)
+    assert np.array_equal(T.normalize_data(x), O.normalize_data(x))
+    xs = np.stack([x[:48000], x[48000:96000] * 0.3 + 0.1])
+    assert np.array_equal(T.normalize_data(xs), O.normalize_data(xs))
+
+
+def test_get_spect_power_vs_golden_and_oracle(engine, golden):
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("get_spect")
+    rec = synth.recording(int(g["seed"]), seconds=12.0)
+    s0 = int(g["seg_start"])
+    x = O.normalize_data(rec[s0:s0 + 144000])
+    got = T.get_spect(x, 48000, 640, False, False, 1750, True, 160, 50, 11000, 4096, 2, False)
+    assert got.shape == (160, 226, 1) and got.dtype == np.float32
+    ref = g["hop640_power"]
+    frac = _match_fraction(got[:, :, 0], ref, 1e-4)
+    worst = float((np.abs(got[:, :, 0] - ref) / np.abs(ref)).max())
+    print("mel power hop640: match@1e-4 = %.5f worst rel = %.3e" % (frac, worst))
+    assert frac >= 0.9
+    assert np.abs(got[:, :, 0] - ref).max() <= 1e-5 * ref.max()
+
+
+def test_get_spect_db_vs_golden(engine, golden):
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("get_spect")
+    rec = synth.recording(int(g["seed"]), seconds=12.0)
+    s0 = int(g["seg_start"])
+    x = O.normalize_data(rec[s0:s0 + 144000])
+    got = T.get_spect(x, 48000, 281, False, False, 1750, True, 160, 50, 11000, 4096, 2, True)
+    assert got.shape == (160, 513, 1)
+    d = np.abs(got[:, :, 0] - g["s1_db"])
+    print("dB: max abs diff %.3e, frac<=1e-2: %.5f" % (d.max(), (d <= 1e-2).mean()))
+    assert (d <= 1e-2).mean() >= 0.9
+    assert d.max() <= 1e-2
+    assert got.max() == 0.0 and got.min() >= -80.0
+
+
+def test_power1_meansub_channels(engine, golden):
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("get_spect")
+    rec = synth.recording(int(g["seed"]), seconds=12.0)
+    s0 = int(g["seg_start"])
+    x = O.normalize_data(rec[s0:s0 + 144000])
+    got = T.get_spect(x, 48000, 281, True, False, 1750, True, 160, 50, 11000, 4096, 1, False, 3)
+    assert got.shape == (160, 513, 3)
+    ref = g["power1_meansub_ch3"]
+    scale = np.abs(ref).max()
+    assert np.abs(got[::4, ::4, :] - ref).max() <= 2e-5 * scale
+
+
+def test_load_samples_matches_oracle_with_ragged_tracks(engine):
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(1234, seconds=12.0)
+    spec = [(0.0, 12.0, 0, 24000), (1.3, 2.1, 800, 3000), (0.05, 0.9, 500, 900), (11.2, 11.95, 2000, 9000),
+            (3.0, 9.7, 100, 12000), (2.0, 5.0, 12000, 15000), (6.1, 9.1000001, 50, 11000)]
+    kw = dict(db_scale=True, normalize=True, **S1)
+    np.random.seed(5)
+    got = T.load_samples(rec, 48000, [T.Signal(*s) for s in spec], 3.0, 1.5, **kw)
+    np.random.seed(5)
+    ref = O.load_samples(rec, 48000, [O.Signal(*s) for s in spec], 3.0, 1.5, **kw)
+    assert [len(t) for t in got] == [len(t) for t in ref]
+    worst, total, ok = 0.0, 0, 0
+    for tg, tr in zip(got, ref):
+        for a, b in zip(tg, tr):
+            assert a.shape == b.shape
+            d = np.abs(a - b)
+            worst = max(worst, float(d.max()))
+            total += d.size
+            ok += int((d <= 1e-2).sum())
+    print("load_samples: %d cells, max |dB diff| %.3e, match %.6f" % (total, worst, ok / total))
+    assert ok / total >= 0.9 and worst <= 1e-2
+
+
+def test_load_samples_golden_reference_segments(engine, golden):
+    """Directly against outputs of the reference's own load_samples (tests/golden)."""
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("load_samples")
+    rec = synth.recording(int(g["rec_seed"]), seconds=12.0)
+    np.random.seed(int(g["seed"]))
+    got = T.load_samples(rec, 48000, [T.Signal(0.0, 12.0, 0, 24000), T.Signal(5.2, 6.0, 1000, 4000)], 3.0, 1.5,
+                         db_scale=True, normalize=True, **S1)
+    assert [len(t) for t in got] == list(g["counts"])
+    for a, b in ((got[0][0], g["t0_first"]), (got[0][-1], g["t0_last"]), (got[1][0], g["t1_only"])):
+        assert np.abs(a[:, :, 0] - b).max() <= 1e-2
+
+
+def test_mel_spec_projection(engine):
+    from audio_analysis_b200 import custommel
+    x = synth.recording(8, seconds=2.0)
+    mag = np.abs(O.stft(x, 4096, 281))
+    for power in (1, 2):
+        got = custommel.mel_spec(mag, 48000, 4096, 281, 160, 50, 11000, 1750, power=power)
+        ref = O.mel_spec(mag, 48000, 4096, 281, 160, 50, 11000, 1750, power=power)
+        assert got.shape == ref.shape
+        assert np.abs(got - ref).max() <= 1e-5 * np.abs(ref).max()
+        assert _match_fraction(got, ref, 1e-4) >= 0.999
+    mag2 = np.abs(O.stft(x, 4800, 281))
+    got = custommel.mel_spec(mag2, 48000, 4800, 281, 120, 50, 11000, 1750, power=1)
+    ref = O.mel_spec(mag2, 48000, 4800, 281, 120, 50, 11000, 1750, power=1)
+    assert _match_fraction(got, ref, 1e-4) >= 0.999
+
+
+def test_device_batch_equals_host_path_and_is_deterministic(engine):
+    import torch
+    from audio_analysis_b200 import identify_tracks as T
+    recs = synth.batch(100, 3, seconds=6.0)
+    segs, counts = T.segment_descriptors(recs.shape[1], 48000, [T.Signal(0, 6.0, 0, 24000)], 3.0, 1.5)
+    allsegs = np.concatenate([segs.copy() for _ in range(3)])
+    for i in range(3):
+        allsegs["pcm_offset"][i * len(segs):(i + 1) * len(segs)] += i * recs.shape[1]
+    plan = T._plan(48000, 4096, 281, 160, 50, 11000, 1750, 144000, 2, True, True)
+    pcm = torch.from_numpy(recs.reshape(-1)).cuda()
+    a = plan.run(pcm, allsegs).cpu().numpy()
+    b = plan.run(pcm, allsegs).cpu().numpy()
+    c = plan.run_host(recs.reshape(-1), allsegs)
+    assert np.array_equal(a, b) and np.array_equal(a, c)
+    ref = O.load_samples(recs[1], 48000, [O.Signal(0, 6.0, 0, 24000)], 3.0, 1.5, db_scale=True, **S1)
+    assert np.abs(a[len(segs)] - ref[0][0][:, :, 0]).max() <= 1e-2
+
+
+def test_error_paths(engine):
+    import ctypes
+    w = np.zeros((160, 2049), np.float32)
+    p = engine.CacParams(48000, 4096, 281, 160, 144000, 3, 1, 1)
+    h = ctypes.c_void_p()
+    rc = engine.lib.cac_plan_create(ctypes.byref(p), w.ctypes.data_as(ctypes.c_void_p), 0, ctypes.byref(h))
+    assert rc == -1 and b"power" in engine.lib.cac_last_error()
+    from audio_analysis_b200 import custommel
+    wide = custommel.mel_f(48000, 160, 50, 20000, 4096, 1750)
+    plan = engine.FeaturePlan(wide, 48000, 4096, 281, 160, 144000)
+    with pytest.raises(engine.CacError):
+        plan.run_host(np.zeros(144000, np.float32), np.array([(0, 144000, 0)], dtype=engine.SEGMENT_DTYPE))
+    good = engine.FeaturePlan(custommel.mel_f(48000, 160, 50, 11000, 4096, 1750), 48000, 4096, 281, 160, 144000)
+    with pytest.raises(engine.CacError):   # descriptor past the end of the pcm buffer
+        good.run_host(np.zeros(1000, np.float32), np.array([(0, 144000, 0)], dtype=engine.SEGMENT_DTYPE))
