@@ -12,7 +12,8 @@
 namespace cac {
 cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st);
 size_t feat_smem_bytes(const FeatArgs& a);
-cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st);
+cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
+                            cudaEvent_t ev1);
 cudaError_t launch_normalize(const float* in, float* out, long long rows, int row_len, cudaStream_t st);
 cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power, cudaStream_t st);
 cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, long long item_len, unsigned* work,
@@ -51,6 +52,8 @@ struct cac_plan {
     cac_segment* d_segs = nullptr; size_t segs_cap = 0;
     float* d_out = nullptr;      size_t out_cap = 0;
     void* d_work = nullptr;      size_t work_cap = 0;
+    // optional CUDA events bracketing the dominant (stft_mel) kernel of the last cac_features_run
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
 extern "C" const char* cac_version(void) { return "cacophony_b200 0.1.0 (sm_100a)"; }
@@ -128,9 +131,31 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
 extern "C" int cac_plan_destroy(cac_plan* plan) {
     if (!plan) return CAC_OK;
     cudaSetDevice(plan->device);
+    if (plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
     cudaFree(plan->d_pcm); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
     delete plan;
+    return CAC_OK;
+}
+
+extern "C" int cac_plan_set_profiling(cac_plan* plan, int enable) {
+    if (!plan) return fail(CAC_ERR_INVALID, "null plan");
+    CUDA_TRY(cudaSetDevice(plan->device));
+    if (enable && !plan->ev0) {
+        CUDA_TRY(cudaEventCreate(&plan->ev0));
+        CUDA_TRY(cudaEventCreate(&plan->ev1));
+    } else if (!enable && plan->ev0) {
+        cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1);
+        plan->ev0 = plan->ev1 = nullptr;
+    }
+    return CAC_OK;
+}
+
+extern "C" int cac_plan_last_kernel_ms(cac_plan* plan, float* ms) {
+    if (!plan || !ms) return fail(CAC_ERR_INVALID, "null argument");
+    if (!plan->ev0) return fail(CAC_ERR_INVALID, "profiling is not enabled on this plan");
+    CUDA_TRY(cudaEventSynchronize(plan->ev1));
+    CUDA_TRY(cudaEventElapsedTime(ms, plan->ev0, plan->ev1));
     return CAC_OK;
 }
 
@@ -166,7 +191,7 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     a.frames_per_stage = plan->frames_per_stage;
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
-    CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st));
+    CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));
     return CAC_OK;
 }
 

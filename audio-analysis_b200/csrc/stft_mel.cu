@@ -273,12 +273,11 @@ __global__ void __launch_bounds__(256) power_to_db_kernel(const float* __restric
     for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
         long long item = i / item_len;
         float ref = __uint_as_float(itemmax[item]);
-        float refdb = 10.0f * log10f(fmaxf(amin, ref));
-        float v = 10.0f * log10f(fmaxf(amin, in[i]));
-        v = v - refdb;
-        // log_spec.max() is exactly 0 when ref is the block maximum, so the clamp floor is -top_db
-        float top = 10.0f * log10f(fmaxf(amin, ref)) - refdb;
-        out[i] = fmaxf(v, top - 80.0f);
+        // explicit _rn intrinsics: no FMA contraction, so the block maximum maps to exactly 0 dB as in numpy
+        float refdb = __fmul_rn(10.0f, log10f(fmaxf(amin, ref)));
+        float v = __fsub_rn(__fmul_rn(10.0f, log10f(fmaxf(amin, in[i]))), refdb);
+        // log_spec.max() is refdb - refdb = 0 when ref is the block maximum, so the floor is -top_db
+        out[i] = fmaxf(v, -80.0f);
     }
 }
 
@@ -351,14 +350,17 @@ size_t feat_smem_bytes(const FeatArgs& a) {
     return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kTileFrames);
 }
 
-cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st) {
+cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
+                            cudaEvent_t ev1) {
     seg_minmax_kernel<<<(unsigned)a.n_segs, 256, 0, st>>>(a.pcm, a.segs, a.segstat, a.segmax, a.seg_len);
     const size_t smem = feat_smem_bytes(a);
     auto kern = (power == 1) ? stft_mel_kernel<1> : stft_mel_kernel<2>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const long long grid = a.n_segs * a.tiles_per_seg;
+    if (ev0) cudaEventRecord(ev0, st);
     kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, st>>>(a);
+    if (ev1) cudaEventRecord(ev1, st);
     if (db_scale) {
         const long long item = (long long)a.n_mels * a.n_frames, total = item * a.n_segs;
         long long blocks = (total + 256 * 8 - 1) / (256 * 8);

@@ -40,6 +40,8 @@ lib.cac_device_count.restype = ctypes.c_int
 lib.cac_plan_create.argtypes = [ctypes.POINTER(CacParams), _vp, ctypes.c_int, ctypes.POINTER(_vp)]
 lib.cac_plan_destroy.argtypes = [_vp]
 lib.cac_plan_frames.argtypes = [_vp]
+lib.cac_plan_set_profiling.argtypes = [_vp, ctypes.c_int]
+lib.cac_plan_last_kernel_ms.argtypes = [_vp, ctypes.POINTER(ctypes.c_float)]
 lib.cac_features_work_bytes.argtypes = [_vp, _i64]
 lib.cac_features_work_bytes.restype = ctypes.c_size_t
 lib.cac_features_run.argtypes = [_vp, _vp, _vp, _i64, _vp, _vp, _vp]
@@ -49,7 +51,7 @@ lib.cac_mel_project_run.argtypes = [_vp, _vp, _i32, _vp, _vp]
 lib.cac_power_to_db_run.argtypes = [_vp, _vp, _i64, _i64, _vp, _vp]
 
 EXPORTS = ["cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
-           "cac_plan_frames", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
+           "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
 
 
@@ -103,6 +105,14 @@ class FeaturePlan:
             self.close()
         except Exception:
             pass
+
+    def set_profiling(self, enable=True):
+        check(lib.cac_plan_set_profiling(self._h, int(enable)))
+
+    def last_kernel_ms(self):
+        ms = ctypes.c_float()
+        check(lib.cac_plan_last_kernel_ms(self._h, ctypes.byref(ms)))
+        return ms.value
 
     # ---- device-resident path -----------------------------------------------------------
     def run(self, pcm, segments, out=None):

@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""Benchmark of the feature hot path (BASELINE.json metric: recording-hours/sec, STFT->mel->dB).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one pass of load_samples' inner loop (normalise -> STFT 4096/281 -> custom mel
+160 -> power_to_db) over the workload of BASELINE.json configs[1]: 1,024 one-minute 48 kHz
+synthetic recordings PER GPU, one whole-file track each = 39 segments -> [39936,160,513] f32.
+Multi-GPU = whole recordings sharded across ranks (weak scaling, no data-path collective).
+Prints ONE JSON line on rank 0.  `--impl reference` times the CPU oracle port of the
+reference path (oracle/oracle_np.py = the reference's numpy/scipy arithmetic) on host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR = 48000
+REC_SECONDS = 60.0
+N_REC = int(os.environ.get("CAC_BENCH_RECORDINGS", "1024"))   # per GPU
+POOL = int(os.environ.get("CAC_BENCH_POOL", "64"))            # unique synthetic recordings per rank
+S1 = dict(hop_length=281, mel_break=1750, n_mels=160, fmin=50, fmax=11000, power=2, db_scale=True,
+          normalize=True, n_fft=4096)
+SEG_LEN, STRIDE = 3.0, 1.5
+ALGO_BYTES_PER_REC = 11_520_000 + 39 * 160 * 513 * 4          # unique PCM in + dB out
+FLOP_PER_REC = 2.65e9
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12              # nominal CUDA-core peak (not measured)
+
+
+def _gen(seed):
+    from audio_analysis_b200 import synth
+    return synth.recording(seed, REC_SECONDS, SR)
+
+
+def make_pool(rank, n):
+    import multiprocessing as mp
+    workers = max(1, min(n, (os.cpu_count() or 8) // max(1, int(os.environ.get("WORLD_SIZE", "1")))))
+    seeds = [1000 + rank * 100003 + i for i in range(n)]
+    if workers == 1:
+        return np.stack([_gen(s) for s in seeds])
+    with mp.get_context("fork").Pool(workers) as p:
+        return np.stack(p.map(_gen, seeds))
+
+
+def _oracle_one(seed):
+    from oracle import oracle_np as O
+    x = _gen(seed)
+    t0 = time.perf_counter()
+    res = O.load_samples(x, SR, [O.Signal(0, REC_SECONDS, 0, 24000)], SEG_LEN, STRIDE, **S1)
+    assert len(res[0]) == 39
+    return time.perf_counter() - t0
+
+
+def cpu_oracle_rate(n_recordings, workers):
+    """rec-hours/s of the CPU oracle on `n_recordings` one-minute recordings with `workers` processes."""
+    import multiprocessing as mp
+    seeds = [5000 + i for i in range(n_recordings)]
+    if workers == 1:
+        t0 = time.perf_counter()
+        for s in seeds:
+            _oracle_one(s)
+        wall = time.perf_counter() - t0
+    else:
+        with mp.get_context("fork").Pool(workers) as p:
+            p.map(_gen, seeds[:workers])          # warm the workers (imports) outside the timing
+            t0 = time.perf_counter()
+            p.map(_oracle_one, seeds, chunksize=1)
+            wall = time.perf_counter() - t0
+    return n_recordings * REC_SECONDS / 3600.0 / wall, wall
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.split(",") for r in open(self.f.name).read().strip().splitlines() if r.count(",") >= 5]
+        os.unlink(self.f.name)
+        sm = [float(r[0]) for r in rows if r[0].strip().replace(".", "").isdigit()]
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(rows[0][1])
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            out["reasons"] = [n for j, n in enumerate(names) if any("Active" == r[2 + j].strip() for r in rows)]
+        return out
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle port) on the host cores, bounded sample."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = max(cores, 8)
+    for _ in range(args.warmup if args.warmup < 1 else 1):
+        cpu_oracle_rate(min(cores, per_step), cores)
+    rates, walls = [], []
+    for _ in range(args.steps):
+        r, w = cpu_oracle_rate(per_step, cores)
+        rates.append(r)
+        walls.append(w)
+    value = per_step * len(walls) * REC_SECONDS / 3600.0 / sum(walls)
+    sample = "%d one-minute recordings per step (39 segments each), %d worker processes" % (per_step, cores)
+    line = {
+        "impl": "reference", "metric": "recording-hours/sec (STFT->mel->dB)", "value": value,
+        "unit": "recording-hours/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1000.0 * sum(walls) / len(walls), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(sample_note=sample),
+        "cpu_baseline": {"value": value, "unit": "recording-hours/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "recording-hours/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(sample_note=None):
+    c = {"workload": "configs[1]: %d x 60 s 48 kHz recordings per GPU, load_samples S1 (n_fft 4096, hop 281, "
+                     "160 mels 50-11000 Hz break 1750, power 2, power_to_db, normalize), 39 segments each" % N_REC,
+         "recordings_per_gpu": N_REC, "segments_per_recording": 39, "unique_recordings_per_gpu": POOL,
+         "l2": "inputs (11.8 GB PCM per GPU) are larger than L2; no flush needed"}
+    if sample_note:
+        c["sample"] = sample_note
+    return c
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from audio_analysis_b200 import engine, identify_tracks as T
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- inputs: a pool of unique synthetic recordings, replicated into distinct HBM buffers -----
+    pool = make_pool(rank, POOL)                                   # [POOL, 2.88M] float32 host
+    n_samp = pool.shape[1]
+    segs1, counts = T.segment_descriptors(n_samp, SR, [T.Signal(0, REC_SECONDS, 0, 24000)], SEG_LEN, STRIDE)
+    nseg1 = len(segs1)
+    assert counts == [39]
+    plan = T._plan(SR, 4096, 281, 160, 50, 11000, 1750, int(SR * SEG_LEN), 2, True, True) if local_rank == 0 else \
+        engine.FeaturePlan(T.custommel._mel_f_cached(SR, 160, 50, 11000, 4096, 1750), SR, 4096, 281, 160,
+                           int(SR * SEG_LEN), power=2, db_scale=True, normalize=True, device=local_rank)
+    plan.set_profiling(True)
+
+    def descriptors(n_rec):
+        s = np.tile(segs1, n_rec)
+        s["pcm_offset"] += np.repeat(np.arange(n_rec, dtype=np.int64) * n_samp, nseg1)
+        return s
+
+    pool_pinned = torch.from_numpy(pool).pin_memory()
+    pool_dev = pool_pinned.to(dev, non_blocking=True)
+    pcm = pool_dev.repeat((N_REC + POOL - 1) // POOL, 1)[:N_REC].contiguous().reshape(-1)   # distinct buffers
+    segs_dev = torch.from_numpy(descriptors(N_REC).view(np.uint8).reshape(-1)).to(dev)
+    out = torch.empty((N_REC * nseg1, 160, plan.n_frames), dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ---------------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        plan.run(pcm, segs_dev, out)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kernel_ms = []
+    ev0.record()
+    for _ in range(args.steps):
+        plan.run(pcm, segs_dev, out)
+    ev1.record()
+    barrier()
+    total_ms = ev0.elapsed_time(ev1)
+    # dominant-kernel duration (events recorded by the library around the fused kernel), one more pass
+    for _ in range(3):
+        plan.run(pcm, segs_dev, out)
+        kernel_ms.append(plan.last_kernel_ms())
+    clocks = sampler.stop() if sampler else None
+    checksum = float(out[:nseg1].double().sum().item())
+
+    # ---- end to end through host buffers (pinned H2D of the inputs + D2H of the result per step) -----
+    chunk = POOL
+    seg_chunk = descriptors(chunk)
+    out_host = np.empty((chunk * nseg1, 160, plan.n_frames), dtype=np.float32)
+    out_host_t = torch.from_numpy(out_host).pin_memory()
+    out_host = out_host_t.numpy()
+    pool_np = pool_pinned.numpy().reshape(-1)
+    n_chunks = (N_REC + chunk - 1) // chunk
+
+    def e2e_step():
+        for _ in range(n_chunks):
+            plan.run_host(pool_np, seg_chunk, out_host)
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 3))
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+
+    # ---- reduce over ranks (max time) -------------------------------------------------------------------
+    t = torch.tensor([total_ms, e2e_s, float(np.median(kernel_ms))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_s, k_ms = (float(v) for v in t.tolist())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    rec_hours = world * N_REC * REC_SECONDS / 3600.0
+    ms_per_step = total_ms / args.steps
+    achieved = ALGO_BYTES_PER_REC * N_REC / (k_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("stft_mel_bytes_per_launch")
+    except Exception:
+        pass
+    line = {
+        "metric": "recording-hours/sec (STFT->mel->dB)", "value": rec_hours / (ms_per_step * 1e-3),
+        "unit": "recording-hours/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(),
+        "e2e": {"value": rec_hours / e2e_s, "unit": "recording-hours/s",
+                "h2d_bytes_per_step": int(n_chunks * (pool_np.nbytes + seg_chunk.nbytes)),
+                "d2h_bytes_per_step": int(n_chunks * out_host.nbytes), "ms_per_step": e2e_s * 1e3,
+                "api": "FeaturePlan.run_host -> cac_features_host, %d recordings per call" % chunk},
+        "gpu_launches": 3 * args.steps,
+        "kernels_per_step": ["seg_minmax_kernel", "stft_mel_kernel<2>", "power_to_db_kernel"],
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "stft_mel_kernel<2>",
+                     "kernel_ms": k_ms, "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback",
+                     "fp32_tflops": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12,
+                     "fp32_frac_of_nominal_peak": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12 / FP32_PEAK_TFLOPS,
+                     "note": "FP32-pipe bound (75-110 flop/B, SURVEY.md 8d); HBM fraction reported as the metric asks"},
+        "clocks": clocks, "checksum_first_recording": checksum,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        n = max(cores, 8)
+        v, wall = cpu_oracle_rate(n, cores)
+        v1, wall1 = cpu_oracle_rate(2, 1)
+        line["cpu_baseline"] = {"value": v, "unit": "recording-hours/s", "cores": cores, "kind": "port",
+                                "sample": "%d one-minute recordings, %d processes, %.1f s wall; single process: %.5f rec-h/s"
+                                          % (n, cores, wall, v1)}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

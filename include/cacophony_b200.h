@@ -71,6 +71,11 @@ int cac_plan_create(const cac_params* params, const float* h_mel_weights, int de
 int cac_plan_destroy(cac_plan* plan);
 /* Frames per segment = 1 + segment_samples / hop_length (librosa.stft, center=True). */
 int cac_plan_frames(const cac_plan* plan);
+/* Measurement hook (no reference counterpart): when enabled, cac_features_run brackets its dominant
+ * kernel (the fused STFT->mel kernel) with CUDA events on the launch stream; cac_plan_last_kernel_ms
+ * waits for that kernel and returns its duration. */
+int cac_plan_set_profiling(cac_plan* plan, int enable);
+int cac_plan_last_kernel_ms(cac_plan* plan, float* ms);
 /* Bytes of device scratch cac_features_run needs for n_segments. */
 size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
 
