@@ -58,17 +58,34 @@ struct ExRead {
 };
 
 // ---- pass 2 twiddles: W2048^(k1*n2), k1 = lane + 32*H  ==  Tw_lane[n2] * W64^(H*n2) ----------
-template <int N2, int H>
-struct Pass2Tw {
-    static __device__ __forceinline__ void run(float (&re)[32], float (&im)[32], const float (&twr)[32],
-                                               const float (&twi)[32]) {
+// Tw_lane[n2] = exp(-2 pi i lane n2 / 2048) is kept as a two-level product A[n2>>3] * B[n2&7]
+// (3 + 7 complex registers instead of 31: keeps the kernel free of register spills).
+struct Twid {
+    float ar[4], ai[4];   // n2 = 0, 8, 16, 24
+    float br[8], bi[8];   // n2 = 0..7
+};
+template <int N2>
+struct Pass2Tw {   // both halves per n2, so the A*B product is formed once and dies immediately
+    static __device__ __forceinline__ void run(float (&z0r)[32], float (&z0i)[32], float (&z1r)[32],
+                                               float (&z1i)[32], const Twid& tw) {
         if constexpr (N2 > 0) {
-            float ar = re[N2], ai = im[N2];
-            if constexpr (H == 1) mul_twiddle<N2, 64>(ar, ai);
-            re[N2] = fmaf(-ai, twi[N2], ar * twr[N2]);
-            im[N2] = fmaf(ar, twi[N2], ai * twr[N2]);
+            constexpr int A = N2 >> 3, B = N2 & 7;
+            float tr, ti;
+            if constexpr (A == 0) { tr = tw.br[B]; ti = tw.bi[B]; }
+            else if constexpr (B == 0) { tr = tw.ar[A]; ti = tw.ai[A]; }
+            else {
+                tr = fmaf(-tw.ai[A], tw.bi[B], tw.ar[A] * tw.br[B]);
+                ti = fmaf(tw.ar[A], tw.bi[B], tw.ai[A] * tw.br[B]);
+            }
+            float xr = z0r[N2], xi = z0i[N2];
+            z0r[N2] = fmaf(-xi, ti, xr * tr);
+            z0i[N2] = fmaf(xr, ti, xi * tr);
+            xr = z1r[N2]; xi = z1i[N2];
+            mul_twiddle<N2, 64>(xr, xi);
+            z1r[N2] = fmaf(-xi, ti, xr * tr);
+            z1i[N2] = fmaf(xr, ti, xi * tr);
         }
-        if constexpr (N2 + 1 < 32) Pass2Tw<N2 + 1, H>::run(re, im, twr, twi);
+        if constexpr (N2 + 1 < 32) Pass2Tw<N2 + 1>::run(z0r, z0i, z1r, z1i, tw);
     }
 };
 
@@ -121,18 +138,19 @@ struct LaneConsts {
 
 // One warp: Hann-windowed 4096-point real FFT of the frame starting at staged sample u0,
 // power spectrum of bins [kmin, kmin+nbins) written to column fcol of the tile.
-template <int POWER>
+template <int POWER, int K2N>
 __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const float* __restrict__ so, int u0,
                                           float* __restrict__ ex, float* __restrict__ ptile, int fcol, int lane,
-                                          const LaneConsts& lc, const float (&twr)[32], const float (&twi)[32],
-                                          int kmin, int nbins) {
+                                          const float* __restrict__ lt, int kmin, int nbins) {
+    // lt: per-lane constants parked in shared memory ([28][32], see stft_mel_kernel) and re-read per
+    // frame so they do not occupy registers next to the 128 data registers of the FFT
     float ar[64], ai[64];
     {
         const float* pe;
         const float* po;
         if (u0 & 1) { pe = so + (u0 >> 1) + lane; po = se + ((u0 + 1) >> 1) + lane; }
         else        { pe = se + (u0 >> 1) + lane; po = so + (u0 >> 1) + lane; }
-        WinLoad<0>::run(ar, ai, pe, po, lc.hcb0, lc.hsb0, lc.hcb1, lc.hsb1);
+        WinLoad<0>::run(ar, ai, pe, po, lt[0 * 32], lt[1 * 32], lt[2 * 32], lt[3 * 32]);
     }
     fft_dif<64>(ar, ai);
 
@@ -146,17 +164,31 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     __syncwarp();
     ExRead<0>::run(z0i, z1i, ex + lane * kExStride);
 
-    Pass2Tw<0, 0>::run(z0r, z0i, twr, twi);
+    {
+        Twid tw;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { tw.ar[j] = lt[(8 + j) * 32]; tw.ai[j] = lt[(12 + j) * 32]; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { tw.br[j] = lt[(16 + j) * 32]; tw.bi[j] = lt[(24 + j) * 32]; }
+        Pass2Tw<0>::run(z0r, z0i, z1r, z1i, tw);
+    }
     fft_dif<32>(z0r, z0i);
-    Pass2Tw<0, 1>::run(z1r, z1i, twr, twi);
     fft_dif<32>(z1r, z1i);
 
     const int partner = (32 - lane) & 31;
-    Untangle<0, 0, 16, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lc.bc0, lc.bs0, ptile, fcol, kmin, nbins);
-    Untangle<0, 1, 16, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lc.bc1, lc.bs1, ptile, fcol, kmin, nbins);
+    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], ptile, fcol, kmin, nbins);
+    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], ptile, fcol, kmin, nbins);
 }
 
-template <int POWER>
+// Correctly rounded x / d from a precomputed reciprocal (one Newton step on the residual): the
+// same result as __fdiv_rn for the normal-range operands normalize_data sees, at 3 FMA-pipe ops.
+__device__ __forceinline__ float div_by(float x, float d, float rcp) {
+    float q = x * rcp;
+    float r = fmaf(-q, d, x);
+    return fmaf(r, rcp, q);
+}
+
+template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
     float* se = smem;                              // even staged samples
@@ -165,77 +197,92 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     float* ptile = exbase + kWarpsPerCta * kExFloats;   // nbins x 32
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long seg = blockIdx.x / a.tiles_per_seg;
-    const int tile = blockIdx.x - (int)(seg * a.tiles_per_seg);
-    const int f0 = tile * kTileFrames;
-    const int tf = min(kTileFrames, a.n_frames - f0);
 
-    const cac_segment sd = a.segs[seg];
-    float mn = 0.f, range = 1.f;
-    if (a.normalize) {
-        float2 st = a.segstat[seg];
-        mn = st.x;
-        range = __fsub_rn(st.y, st.x);
-    }
-
-    LaneConsts lc;
-    {
+    // per-lane constants -> shared memory table lt[row][lane] (rows: 0-3 window, 4-7 untangle, 8-31 twiddles)
+    float* ltab = ptile + (size_t)a.nbins * kTileFrames;
+    if (warp == 0) {
         float s, c;
-        sincospif((float)(2 * lane) / 2048.0f, &s, &c);      lc.hcb0 = 0.5f * c; lc.hsb0 = 0.5f * s;
-        sincospif((float)(2 * lane + 1) / 2048.0f, &s, &c);  lc.hcb1 = 0.5f * c; lc.hsb1 = 0.5f * s;
-        sincospif((float)lane / 2048.0f, &s, &c);            lc.bc0 = c; lc.bs0 = s;
-        sincospif((float)(lane + 32) / 2048.0f, &s, &c);     lc.bc1 = c; lc.bs1 = s;
+        sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
+        sincospif((float)(2 * lane + 1) / 2048.0f, &s, &c);  ltab[2 * 32 + lane] = 0.5f * c; ltab[3 * 32 + lane] = 0.5f * s;
+        sincospif((float)lane / 2048.0f, &s, &c);            ltab[4 * 32 + lane] = c; ltab[5 * 32 + lane] = s;
+        sincospif((float)(lane + 32) / 2048.0f, &s, &c);     ltab[6 * 32 + lane] = c; ltab[7 * 32 + lane] = s;
+        for (int j = 0; j < 4; ++j) {                         // exp(-2 pi i lane (8j) / 2048)
+            sincospif((float)(lane * 8 * j) / 1024.0f, &s, &c);
+            ltab[(8 + j) * 32 + lane] = c; ltab[(12 + j) * 32 + lane] = -s;
+        }
+        for (int j = 0; j < 8; ++j) {                         // exp(-2 pi i lane j / 2048)
+            sincospif((float)(lane * j) / 1024.0f, &s, &c);
+            ltab[(16 + j) * 32 + lane] = c; ltab[(24 + j) * 32 + lane] = -s;
+        }
     }
-    float twr[32], twi[32];
-#pragma unroll
-    for (int n2 = 0; n2 < 32; ++n2) {
-        float s, c;
-        sincospif((float)(lane * n2) / 1024.0f, &s, &c);     // exp(-2 pi i lane n2 / 2048)
-        twr[n2] = c;
-        twi[n2] = -s;
-    }
-
+    const float* lt = ltab + lane;
     float* ex = exbase + warp * kExFloats;
-    for (int fs0 = 0; fs0 < tf; fs0 += a.frames_per_stage) {
-        const int nfs = min(a.frames_per_stage, tf - fs0);
-        const int p0 = (f0 + fs0) * a.hop;                    // padded-signal coordinate of stage start
-        const int len = (nfs - 1) * a.hop + kNfft;
-        __syncthreads();
-        for (int u = tid; u < len; u += kWarpsPerCta * 32) {
-            int s = p0 + u - kNfft / 2;                       // sample index inside the segment
-            float v = 0.f;
-            if (s >= 0 && s < a.seg_len) {
-                int r = s - sd.pad_left;
-                if (r >= 0 && r < sd.n_valid) v = __ldg(a.pcm + sd.pcm_offset + r);
-                if (a.normalize) v = normalize_sample(v, mn, range);
-            }
-            ((u & 1) ? so : se)[u >> 1] = v;
-        }
-        __syncthreads();
-        for (int fi = warp; fi < nfs; fi += kWarpsPerCta)
-            fft_frame<POWER>(se, so, fi * a.hop, ex, ptile, fs0 + fi, lane, lc, twr, twi, a.kmin, a.nbins);
-    }
-    __syncthreads();
+    const long long n_tiles = a.n_segs * a.tiles_per_seg;
 
-    // banded mel projection: lane = frame of the tile, warp w owns mel rows w, w+8, ...
-    float vmax = 0.f;
-    float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
-    for (int m = warp; m < a.n_mels; m += kWarpsPerCta) {
-        const int kk0 = c_bands.start[m] - a.kmin;
-        const int len = c_bands.len[m];
-        const float* w = c_weights + c_bands.off[m];
-        float acc = 0.f;
-        for (int t = 0; t < len; ++t) {
-            int kk = kk0 + t;
-            acc = fmaf(w[t], ptile[kk * kTileFrames + ((lane + kk) & 31)], acc);
+    // persistent CTA: one per SM, tiles (32 frames of one segment) taken round-robin
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const long long seg = t / a.tiles_per_seg;
+        const int tile = (int)(t - seg * a.tiles_per_seg);
+        const int f0 = tile * kTileFrames;
+        const int tf = min(kTileFrames, a.n_frames - f0);
+        const cac_segment sd = a.segs[seg];
+        float mn = 0.f, range = 1.f, rcp = 1.f;
+        if (a.normalize) {
+            float2 st = a.segstat[seg];
+            mn = st.x;
+            range = __fsub_rn(st.y, st.x);
+            rcp = __frcp_rn(range);
         }
-        if (lane < tf) {
-            outseg[(size_t)m * a.n_frames + f0 + lane] = acc;
-            vmax = fmaxf(vmax, acc);
+        const bool fast_div = range > 1e-30f && range < 1e30f;
+        const float* __restrict__ src = a.pcm + sd.pcm_offset;
+
+        for (int fs0 = 0; fs0 < tf; fs0 += a.frames_per_stage) {
+            const int nfs = min(a.frames_per_stage, tf - fs0);
+            const int p0 = (f0 + fs0) * a.hop;                // padded-signal coordinate of stage start
+            const int len = (nfs - 1) * a.hop + kNfft;
+            __syncthreads();                                  // previous consumers of se/so/ptile are done
+            for (int u = tid; u < len; u += kWarpsPerCta * 32) {
+                int s = p0 + u - kNfft / 2;                   // sample index inside the segment
+                float v = 0.f;
+                if (s >= 0 && s < a.seg_len) {
+                    int r = s - sd.pad_left;
+                    if (r >= 0 && r < sd.n_valid) v = __ldg(src + r);
+                    if (a.normalize) {
+                        float x = __fsub_rn(v, mn);
+                        x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
+                        x = __fadd_rn(x, 0.000001f);
+                        v = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
+                    }
+                }
+                ((u & 1) ? so : se)[u >> 1] = v;
+            }
+            __syncthreads();
+#pragma unroll 1
+            for (int fi = warp; fi < nfs; fi += kWarpsPerCta)
+                fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, ptile, fs0 + fi, lane, lt, a.kmin, a.nbins);
         }
+        __syncthreads();
+
+        // banded mel projection: lane = frame of the tile, warp w owns mel rows w, w+8, ...
+        float vmax = 0.f;
+        float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
+        for (int m = warp; m < a.n_mels; m += kWarpsPerCta) {
+            const int kk0 = c_bands.start[m] - a.kmin;
+            const int len = c_bands.len[m];
+            const float* w = c_weights + c_bands.off[m];
+            float acc = 0.f;
+            for (int i = 0; i < len; ++i) {
+                int kk = kk0 + i;
+                acc = fmaf(w[i], ptile[kk * kTileFrames + ((lane + kk) & 31)], acc);
+            }
+            if (lane < tf) {
+                outseg[(size_t)m * a.n_frames + f0 + lane] = acc;
+                vmax = fmaxf(vmax, acc);
+            }
+        }
+        vmax = warp_max(vmax);
+        if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
     }
-    vmax = warp_max(vmax);
-    if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
 }
 
 // ---- per-segment min / max of the zero-padded segment (normalize_data's reductions) ---------
@@ -347,17 +394,26 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kTileFrames);
+    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kTileFrames +
+                            32 * 32);
 }
 
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
                             cudaEvent_t ev1) {
     seg_minmax_kernel<<<(unsigned)a.n_segs, 256, 0, st>>>(a.pcm, a.segs, a.segstat, a.segmax, a.seg_len);
     const size_t smem = feat_smem_bytes(a);
-    auto kern = (power == 1) ? stft_mel_kernel<1> : stft_mel_kernel<2>;
+    // K2N = number of 64-bin blocks the untangle stage must produce (bins < 64*K2N)
+    const int k2n = (a.kmin + a.nbins - 1) / 64 + 1;
+    void (*kern)(const FeatArgs);
+    if (k2n <= 15) kern = (power == 1) ? stft_mel_kernel<1, 15> : stft_mel_kernel<2, 15>;
+    else           kern = (power == 1) ? stft_mel_kernel<1, 16> : stft_mel_kernel<2, 16>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    const long long grid = a.n_segs * a.tiles_per_seg;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long grid = a.n_segs * a.tiles_per_seg;
+    if (grid > sms) grid = sms;                               // persistent: one CTA per SM
     if (ev0) cudaEventRecord(ev0, st);
     kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, st>>>(a);
     if (ev1) cudaEventRecord(ev1, st);
