@@ -21,6 +21,7 @@ constexpr int kExStride = 33;                 // floats per exchange row (odd ->
 constexpr int kExFloats = 64 * kExStride;     // one plane (re or im) of one warp's exchange buffer
 constexpr int kWarpsPerCta = 8;
 constexpr int kTileFrames = 32;
+constexpr int kPStride = 33;                  // floats per power-spectrum row (bin): odd -> conflict-free both ways
 
 // ---- pass 1 input: 64 complex points z[32*i + lane] = (x[2n], x[2n+1]) * Hann ------------
 // Hann(s) = 0.5 - 0.5 cos(2 pi s / 4096) with s = 64*i + (2*lane + e): the cosine of the sum is
@@ -124,7 +125,7 @@ struct Untangle {
         float p = fmaf(xr, xr, xi * xi);
         if constexpr (POWER == 1) p = sqrtf(p);
         int kk = lane + 32 * H + 64 * K2 - kmin;
-        if (kk >= 0 && kk < nbins) ptile[kk * kTileFrames + ((fcol + kk) & 31)] = p;
+        if (kk >= 0 && kk < nbins) ptile[kk * kPStride + fcol] = p;
         if constexpr (K2 + 1 < K2N)
             Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, ptile, fcol, kmin,
                                                  nbins);
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // per-lane constants -> shared memory table lt[row][lane] (rows: 0-3 window, 4-7 untangle, 8-31 twiddles)
-    float* ltab = ptile + (size_t)a.nbins * kTileFrames;
+    float* ltab = ptile + (size_t)a.nbins * kPStride;
     if (warp == 0) {
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
@@ -241,20 +242,29 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             const int p0 = (f0 + fs0) * a.hop;                // padded-signal coordinate of stage start
             const int len = (nfs - 1) * a.hop + kNfft;
             __syncthreads();                                  // previous consumers of se/so/ptile are done
-            for (int u = tid; u < len; u += kWarpsPerCta * 32) {
-                int s = p0 + u - kNfft / 2;                   // sample index inside the segment
-                float v = 0.f;
-                if (s >= 0 && s < a.seg_len) {
-                    int r = s - sd.pad_left;
-                    if (r >= 0 && r < sd.n_valid) v = __ldg(src + r);
+            // 8 independent global loads in flight per thread before any of them is consumed
+            for (int u0 = tid; u0 < len; u0 += 8 * kWarpsPerCta * 32) {
+                float v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int u = u0 + j * kWarpsPerCta * 32;
+                    const int r = p0 + u - kNfft / 2 - sd.pad_left;     // index into the real samples
+                    v[j] = (u < len && r >= 0 && r < sd.n_valid) ? __ldg(src + r) : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int u = u0 + j * kWarpsPerCta * 32;
+                    const int sidx = p0 + u - kNfft / 2;                // sample index inside the segment
+                    float x = v[j];
                     if (a.normalize) {
-                        float x = __fsub_rn(v, mn);
+                        x = __fsub_rn(x, mn);
                         x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
                         x = __fadd_rn(x, 0.000001f);
-                        v = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
+                        x = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
                     }
+                    if (sidx < 0 || sidx >= a.seg_len) x = 0.f;         // librosa's centre padding stays zero
+                    if (u < len) ((u & 1) ? so : se)[u >> 1] = x;
                 }
-                ((u & 1) ? so : se)[u >> 1] = v;
             }
             __syncthreads();
 #pragma unroll 1
@@ -270,11 +280,16 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             const int kk0 = c_bands.start[m] - a.kmin;
             const int len = c_bands.len[m];
             const float* w = c_weights + c_bands.off[m];
+            const float* prow = ptile + kk0 * kPStride + lane;
             float acc = 0.f;
-            for (int i = 0; i < len; ++i) {
-                int kk = kk0 + i;
-                acc = fmaf(w[i], ptile[kk * kTileFrames + ((lane + kk) & 31)], acc);
+            int i = 0;
+            for (; i + 4 <= len; i += 4) {
+                acc = fmaf(w[i], prow[i * kPStride], acc);
+                acc = fmaf(w[i + 1], prow[(i + 1) * kPStride], acc);
+                acc = fmaf(w[i + 2], prow[(i + 2) * kPStride], acc);
+                acc = fmaf(w[i + 3], prow[(i + 3) * kPStride], acc);
             }
+            for (; i < len; ++i) acc = fmaf(w[i], prow[i * kPStride], acc);
             if (lane < tf) {
                 outseg[(size_t)m * a.n_frames + f0 + lane] = acc;
                 vmax = fmaxf(vmax, acc);
@@ -394,7 +409,7 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kTileFrames +
+    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kPStride +
                             32 * 32);
 }
 
