@@ -114,12 +114,14 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     plan->kmax = kmax;
     // frames staged per round: largest multiple of 8 that fits the 227 KB shared-memory budget
     plan->frames_per_stage = 0;
-    for (int fs = 32; fs >= 8; fs -= 8) {
+    for (int fs = 16; fs >= 8; fs -= 8) {
         int stage_len = (fs - 1) * p.hop_length + 4096;
         int half = (((stage_len + 1) / 2 + 1 + 31) / 32) * 32 + 16;
         FeatArgs a{};
         a.stage_half = half;
         a.nbins = kmax - kmin + 1;
+        a.n_taps = (int)plan->weights.size();
+        a.n_mels = p.n_mels;
         if (feat_smem_bytes(a) <= 227 * 1024) { plan->frames_per_stage = fs; plan->stage_half = half; break; }
     }
     if (!plan->frames_per_stage && plan->fused_unsupported.empty())
@@ -171,7 +173,7 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     if (!plan || !d_pcm || !d_segs || !d_out || !d_work) return fail(CAC_ERR_INVALID, "null argument");
     if (!plan->fused_unsupported.empty()) return fail(CAC_ERR_INVALID, plan->fused_unsupported);
     if (n == 0) return CAC_OK;
-    if (n < 0 || n * ((plan->n_frames + 31) / 32) > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_segments out of range");
+    if (n < 0 || n > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_segments out of range");
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(plan->device));
     int rc = ensure_constants(plan, st);
@@ -187,8 +189,9 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     a.n_mels = plan->p.n_mels;
     a.kmin = plan->kmin;
     a.nbins = plan->kmax - plan->kmin + 1;
-    a.tiles_per_seg = (plan->n_frames + 31) / 32;
     a.frames_per_stage = plan->frames_per_stage;
+    a.stages_per_seg = (plan->n_frames + plan->frames_per_stage - 1) / plan->frames_per_stage;
+    a.n_taps = (int)plan->weights.size();
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
     CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));

@@ -30,8 +30,9 @@ struct FeatArgs {
     int n_mels;
     int kmin;              // lowest FFT bin any band touches
     int nbins;             // kmax - kmin + 1
-    int tiles_per_seg;     // ceil(n_frames / 32)
-    int frames_per_stage;  // multiple of 8
+    int stages_per_seg;    // ceil(n_frames / frames_per_stage)
+    int frames_per_stage;  // multiple of 8: frames staged (and transformed) per round
+    int n_taps;            // packed filterbank weights
     int stage_half;        // floats reserved for each of the even/odd sample planes
     int normalize;
 };

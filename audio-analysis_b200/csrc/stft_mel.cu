@@ -97,8 +97,8 @@ template <int K2, int H, int K2N, int POWER>
 struct Untangle {
     static __device__ __forceinline__ void run(const float (&z0r)[32], const float (&z0i)[32],
                                                const float (&z1r)[32], const float (&z1i)[32], int lane,
-                                               int partner, float bc, float bs, float* ptile, int fcol,
-                                               int kmin, int nbins) {
+                                               int partner, float bc, float bs, float* pbuf, int kmin,
+                                               int nbins) {
         constexpr int pown = out_pos(32, K2);
         constexpr int psend = out_pos(32, 31 - K2);
         constexpr int psend0 = out_pos(32, (32 - K2) & 31);
@@ -125,10 +125,9 @@ struct Untangle {
         float p = fmaf(xr, xr, xi * xi);
         if constexpr (POWER == 1) p = sqrtf(p);
         int kk = lane + 32 * H + 64 * K2 - kmin;
-        if (kk >= 0 && kk < nbins) ptile[kk * kPStride + fcol] = p;
+        if (kk >= 0 && kk < nbins) pbuf[kk] = p;
         if constexpr (K2 + 1 < K2N)
-            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, ptile, fcol, kmin,
-                                                 nbins);
+            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, pbuf, kmin, nbins);
     }
 };
 
@@ -138,10 +137,10 @@ struct LaneConsts {
 };
 
 // One warp: Hann-windowed 4096-point real FFT of the frame starting at staged sample u0,
-// power spectrum of bins [kmin, kmin+nbins) written to column fcol of the tile.
+// power spectrum of bins [kmin, kmin+nbins) written to the warp's own buffer pbuf[bin - kmin].
 template <int POWER, int K2N>
 __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const float* __restrict__ so, int u0,
-                                          float* __restrict__ ex, float* __restrict__ ptile, int fcol, int lane,
+                                          float* __restrict__ ex, float* __restrict__ pbuf, int lane,
                                           const float* __restrict__ lt, int kmin, int nbins) {
     // lt: per-lane constants parked in shared memory ([28][32], see stft_mel_kernel) and re-read per
     // frame so they do not occupy registers next to the 128 data registers of the FFT
@@ -177,8 +176,8 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     fft_dif<32>(z1r, z1i);
 
     const int partner = (32 - lane) & 31;
-    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], ptile, fcol, kmin, nbins);
-    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], ptile, fcol, kmin, nbins);
+    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], pbuf, kmin, nbins);
+    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], pbuf, kmin, nbins);
 }
 
 // Correctly rounded x / d from a precomputed reciprocal (one Newton step on the residual): the
@@ -189,19 +188,73 @@ __device__ __forceinline__ float div_by(float x, float d, float rcp) {
     return fmaf(r, rcp, q);
 }
 
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    int nbytes = valid ? 4 : 0;                    // 0 source bytes -> the 4 destination bytes are zero-filled
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Shared-memory carve-up of stft_mel_kernel (floats unless noted); the launcher uses the same function.
+struct FeatSmem {
+    int stage[2];      // two staging buffers, each 2 planes (even / odd samples) of stage_half floats
+    int ex;            // 8 warps x kExFloats
+    int pbuf;          // 8 warps x nbins_pad
+    int nbins_pad;
+    int wts;           // packed band weights
+    int bands;         // int: start[n_mels], len[n_mels], off[n_mels], gmax[(n_mels+31)/32]
+    int ltab;          // 32 x 32
+    int total;
+};
+__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int nbins, int n_taps, int n_mels) {
+    FeatSmem L;
+    int o = 0;
+    L.stage[0] = o; o += 2 * stage_half;
+    L.stage[1] = o; o += 2 * stage_half;
+    L.ex = o; o += kWarpsPerCta * kExFloats;
+    L.nbins_pad = (nbins + 31) / 32 * 32;
+    L.pbuf = o; o += kWarpsPerCta * L.nbins_pad;
+    L.wts = o; o += (n_taps + 3) / 4 * 4;
+    L.bands = o; o += 3 * n_mels + (n_mels + 31) / 32;
+    o = (o + 31) / 32 * 32;
+    L.ltab = o; o += 32 * 32;
+    L.total = o;
+    return L;
+}
+
+// Persistent kernel, one CTA (8 warps) per SM.  Work unit = a "stage": frames_per_stage consecutive
+// frames of one segment.  The raw samples of stage q+G are fetched with cp.async (zero-filled
+// outside the real samples) into the second staging buffer while the warps transform stage q;
+// each warp owns whole frames: FFT -> power spectrum (own buffer) -> banded mel gather -> store.
 template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
-    float* se = smem;                              // even staged samples
-    float* so = se + a.stage_half;                 // odd staged samples
-    float* exbase = so + a.stage_half;             // 8 x kExFloats
-    float* ptile = exbase + kWarpsPerCta * kExFloats;   // nbins x 32
-
+    const FeatSmem L = feat_smem_layout(a.stage_half, a.nbins, a.n_taps, a.n_mels);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* ex = smem + L.ex + warp * kExFloats;
+    float* pbuf = smem + L.pbuf + warp * L.nbins_pad;
+    float* wts = smem + L.wts;
+    int* bstart = reinterpret_cast<int*>(smem + L.bands);
+    int* blen = bstart + a.n_mels;
+    int* boff = blen + a.n_mels;
+    int* gmax = boff + a.n_mels;
+    float* ltab = smem + L.ltab;
+    const int n_groups = (a.n_mels + 31) / 32;
 
-    // per-lane constants -> shared memory table lt[row][lane] (rows: 0-3 window, 4-7 untangle, 8-31 twiddles)
-    float* ltab = ptile + (size_t)a.nbins * kPStride;
-    if (warp == 0) {
+    // ---- one-time tables ------------------------------------------------------------------------
+    for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = c_weights[i];
+    for (int m = tid; m < a.n_mels; m += kWarpsPerCta * 32) {
+        bstart[m] = c_bands.start[m] - a.kmin;
+        blen[m] = c_bands.len[m];
+        boff[m] = c_bands.off[m];
+    }
+    if (tid < n_groups) {
+        int g = 0;
+        for (int m = tid * 32; m < min(a.n_mels, tid * 32 + 32); ++m) g = max(g, (int)c_bands.len[m]);
+        gmax[tid] = g;
+    }
+    if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
         sincospif((float)(2 * lane + 1) / 2048.0f, &s, &c);  ltab[2 * 32 + lane] = 0.5f * c; ltab[3 * 32 + lane] = 0.5f * s;
@@ -217,83 +270,82 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         }
     }
     const float* lt = ltab + lane;
-    float* ex = exbase + warp * kExFloats;
-    const long long n_tiles = a.n_segs * a.tiles_per_seg;
 
-    // persistent CTA: one per SM, tiles (32 frames of one segment) taken round-robin
-    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const long long seg = t / a.tiles_per_seg;
-        const int tile = (int)(t - seg * a.tiles_per_seg);
-        const int f0 = tile * kTileFrames;
-        const int tf = min(kTileFrames, a.n_frames - f0);
+    const long long n_stages = a.n_segs * a.stages_per_seg;
+    // geometry of stage q: segment, first frame, frame count, first padded-signal coordinate, length
+    auto issue_stage = [&](long long q, int buf) {
+        const long long seg = q / a.stages_per_seg;
+        const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
+        const int nfs = min(a.frames_per_stage, a.n_frames - f0);
+        const int len = (nfs - 1) * a.hop + kNfft;
         const cac_segment sd = a.segs[seg];
-        float mn = 0.f, range = 1.f, rcp = 1.f;
-        if (a.normalize) {
-            float2 st = a.segstat[seg];
-            mn = st.x;
-            range = __fsub_rn(st.y, st.x);
-            rcp = __frcp_rn(range);
+        const float* src = a.pcm + sd.pcm_offset;
+        const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;  // real-sample index of staged element 0
+        float* pe = smem + L.stage[buf];
+        float* po = pe + a.stage_half;
+        for (int u = tid; u < len; u += kWarpsPerCta * 32) {
+            const int r = r0 + u;
+            const bool valid = r >= 0 && r < sd.n_valid;
+            cp_async4(((u & 1) ? po : pe) + (u >> 1), valid ? src + r : src, valid);
         }
-        const bool fast_div = range > 1e-30f && range < 1e30f;
-        const float* __restrict__ src = a.pcm + sd.pcm_offset;
+        cp_async_commit();
+    };
 
-        for (int fs0 = 0; fs0 < tf; fs0 += a.frames_per_stage) {
-            const int nfs = min(a.frames_per_stage, tf - fs0);
-            const int p0 = (f0 + fs0) * a.hop;                // padded-signal coordinate of stage start
-            const int len = (nfs - 1) * a.hop + kNfft;
-            __syncthreads();                                  // previous consumers of se/so/ptile are done
-            // 8 independent global loads in flight per thread before any of them is consumed
-            for (int u0 = tid; u0 < len; u0 += 8 * kWarpsPerCta * 32) {
-                float v[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int u = u0 + j * kWarpsPerCta * 32;
-                    const int r = p0 + u - kNfft / 2 - sd.pad_left;     // index into the real samples
-                    v[j] = (u < len && r >= 0 && r < sd.n_valid) ? __ldg(src + r) : 0.f;
-                }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int u = u0 + j * kWarpsPerCta * 32;
-                    const int sidx = p0 + u - kNfft / 2;                // sample index inside the segment
-                    float x = v[j];
-                    if (a.normalize) {
-                        x = __fsub_rn(x, mn);
-                        x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
-                        x = __fadd_rn(x, 0.000001f);
-                        x = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
-                    }
-                    if (sidx < 0 || sidx >= a.seg_len) x = 0.f;         // librosa's centre padding stays zero
-                    if (u < len) ((u & 1) ? so : se)[u >> 1] = x;
-                }
+    long long q = blockIdx.x;
+    if (q < n_stages) issue_stage(q, 0);
+    for (int it = 0; q < n_stages; q += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const long long seg = q / a.stages_per_seg;
+        const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
+        const int nfs = min(a.frames_per_stage, a.n_frames - f0);
+        const int len = (nfs - 1) * a.hop + kNfft;
+        float* se = smem + L.stage[buf];
+        float* so = se + a.stage_half;
+
+        cp_async_wait_all();
+        __syncthreads();                       // stage q has landed; everyone is done with stage q-G
+        if (q + gridDim.x < n_stages) issue_stage(q + gridDim.x, buf ^ 1);
+
+        if (a.normalize) {                     // normalize_data in place, exact float32 op order
+            const float2 st = a.segstat[seg];
+            const float mn = st.x, range = __fsub_rn(st.y, st.x), rcp = __frcp_rn(range);
+            const bool fast_div = range > 1e-30f && range < 1e30f;
+            const int s0 = f0 * a.hop - kNfft / 2;            // segment sample index of staged element 0
+            const int ulo = max(0, -s0), uhi = min(len, a.seg_len - s0);   // librosa's centre padding stays 0
+            for (int u = ulo + tid; u < uhi; u += kWarpsPerCta * 32) {
+                float* p = ((u & 1) ? so : se) + (u >> 1);
+                float x = __fsub_rn(*p, mn);
+                x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
+                x = __fadd_rn(x, 0.000001f);
+                *p = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
             }
             __syncthreads();
-#pragma unroll 1
-            for (int fi = warp; fi < nfs; fi += kWarpsPerCta)
-                fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, ptile, fs0 + fi, lane, lt, a.kmin, a.nbins);
         }
-        __syncthreads();
 
-        // banded mel projection: lane = frame of the tile, warp w owns mel rows w, w+8, ...
         float vmax = 0.f;
         float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
-        for (int m = warp; m < a.n_mels; m += kWarpsPerCta) {
-            const int kk0 = c_bands.start[m] - a.kmin;
-            const int len = c_bands.len[m];
-            const float* w = c_weights + c_bands.off[m];
-            const float* prow = ptile + kk0 * kPStride + lane;
-            float acc = 0.f;
-            int i = 0;
-            for (; i + 4 <= len; i += 4) {
-                acc = fmaf(w[i], prow[i * kPStride], acc);
-                acc = fmaf(w[i + 1], prow[(i + 1) * kPStride], acc);
-                acc = fmaf(w[i + 2], prow[(i + 2) * kPStride], acc);
-                acc = fmaf(w[i + 3], prow[(i + 3) * kPStride], acc);
+#pragma unroll 1
+        for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
+            fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt, a.kmin, a.nbins);
+            __syncwarp();
+            // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
+#pragma unroll 1
+            for (int g = 0; g < n_groups; ++g) {
+                const int m = g * 32 + lane;
+                const bool live = m < a.n_mels;
+                const int len_m = live ? blen[m] : 0;
+                const float* w = wts + (live ? boff[m] : 0);
+                const float* pp = pbuf + (live ? bstart[m] : 0);
+                const int gm = gmax[g];
+                float acc = 0.f;
+                for (int i = 0; i < gm; ++i)
+                    if (i < len_m) acc = fmaf(w[i], pp[i], acc);
+                if (live) {
+                    outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
+                    vmax = fmaxf(vmax, acc);
+                }
             }
-            for (; i < len; ++i) acc = fmaf(w[i], prow[i * kPStride], acc);
-            if (lane < tf) {
-                outseg[(size_t)m * a.n_frames + f0 + lane] = acc;
-                vmax = fmaxf(vmax, acc);
-            }
+            __syncwarp();
         }
         vmax = warp_max(vmax);
         if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
@@ -409,8 +461,7 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * ((size_t)2 * a.stage_half + (size_t)kWarpsPerCta * kExFloats + (size_t)a.nbins * kPStride +
-                            32 * 32);
+    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.nbins, a.n_taps, a.n_mels).total;
 }
 
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
@@ -427,7 +478,7 @@ cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStre
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    long long grid = a.n_segs * a.tiles_per_seg;
+    long long grid = a.n_segs * a.stages_per_seg;
     if (grid > sms) grid = sms;                               // persistent: one CTA per SM
     if (ev0) cudaEventRecord(ev0, st);
     kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, st>>>(a);
