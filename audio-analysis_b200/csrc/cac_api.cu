@@ -112,11 +112,13 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     else if (kmax >= 1024) plan->fused_unsupported = "fused STFT->mel kernel covers FFT bins < 1024 (fmax < sr/4)";
     plan->kmin = kmin;
     plan->kmax = kmax;
-    // frames staged per round: largest multiple of 8 that fits the 227 KB shared-memory budget
+    // frames staged per round: a multiple of the 12 warps per CTA when it fits the 227 KB of shared
+    // memory (hop 281 -> 12), else the largest smaller count (some warps then idle during the FFTs)
     plan->frames_per_stage = 0;
-    for (int fs = 16; fs >= 8; fs -= 8) {
+    static const int kFsChoices[] = {24, 12, 10, 8, 6, 4, 3, 2, 1};
+    for (int fs : kFsChoices) {
         int stage_len = (fs - 1) * p.hop_length + 4096;
-        int half = (((stage_len + 1) / 2 + 1 + 31) / 32) * 32 + 16;
+        int half = (((stage_len + 8 + 1) / 2 + 1 + 31) / 32) * 32 + 16;   // also sizes the raw buffer (stage_len + 8)
         FeatArgs a{};
         a.stage_half = half;
         a.nbins = kmax - kmin + 1;
@@ -173,6 +175,7 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     if (!plan || !d_pcm || !d_segs || !d_out || !d_work) return fail(CAC_ERR_INVALID, "null argument");
     if (!plan->fused_unsupported.empty()) return fail(CAC_ERR_INVALID, plan->fused_unsupported);
     if (n == 0) return CAC_OK;
+    if (((uintptr_t)d_pcm & 15) != 0) return fail(CAC_ERR_INVALID, "d_pcm must be 16-byte aligned");
     if (n < 0 || n > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_segments out of range");
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(plan->device));

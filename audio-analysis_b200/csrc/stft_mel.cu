@@ -19,7 +19,7 @@ __constant__ float c_weights[kMaxTaps];
 constexpr int kNfft = 4096;
 constexpr int kExStride = 33;                 // floats per exchange row (odd -> conflict-free transpose)
 constexpr int kExFloats = 64 * kExStride;     // one plane (re or im) of one warp's exchange buffer
-constexpr int kWarpsPerCta = 8;
+constexpr int kWarpsPerCta = 12;               // 12 warps x 168 registers fill the register file
 constexpr int kTileFrames = 32;
 constexpr int kPStride = 33;                  // floats per power-spectrum row (bin): odd -> conflict-free both ways
 
@@ -193,12 +193,18 @@ __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bo
     int nbytes = valid ? 4 : 0;                    // 0 source bytes -> the 4 destination bytes are zero-filled
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
 }
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool valid) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    int nbytes = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Shared-memory carve-up of stft_mel_kernel (floats unless noted); the launcher uses the same function.
 struct FeatSmem {
-    int stage[2];      // two staging buffers, each 2 planes (even / odd samples) of stage_half floats
+    int raw;           // raw samples of the next stage as fetched by cp.async (stage_len + 8 floats)
+    int stage;         // 2 planes (even / odd samples) of stage_half floats: normalised samples of this stage
     int ex;            // 8 warps x kExFloats
     int pbuf;          // 8 warps x nbins_pad
     int nbins_pad;
@@ -210,8 +216,8 @@ struct FeatSmem {
 __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int nbins, int n_taps, int n_mels) {
     FeatSmem L;
     int o = 0;
-    L.stage[0] = o; o += 2 * stage_half;
-    L.stage[1] = o; o += 2 * stage_half;
+    L.raw = o; o += 2 * stage_half;
+    L.stage = o; o += 2 * stage_half;
     L.ex = o; o += kWarpsPerCta * kExFloats;
     L.nbins_pad = (nbins + 31) / 32 * 32;
     L.pbuf = o; o += kWarpsPerCta * L.nbins_pad;
@@ -272,55 +278,82 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     const float* lt = ltab + lane;
 
     const long long n_stages = a.n_segs * a.stages_per_seg;
-    // geometry of stage q: segment, first frame, frame count, first padded-signal coordinate, length
-    auto issue_stage = [&](long long q, int buf) {
+    float* raw = smem + L.raw;
+    float* se = smem + L.stage;
+    float* so = se + a.stage_half;
+    // Stage q = frames [f0, f0+nfs) of one segment = staged elements u in [0, len), element u being real
+    // sample r0+u of the segment's PCM (zero outside [0, n_valid)).  raw[j] holds element u = j - shift with
+    // shift chosen so that raw[4i] is 16-byte aligned in global memory -> one 16-byte cp.async per 4 samples.
+    auto issue_stage = [&](long long q) {
         const long long seg = q / a.stages_per_seg;
         const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         const int len = (nfs - 1) * a.hop + kNfft;
         const cac_segment sd = a.segs[seg];
         const float* src = a.pcm + sd.pcm_offset;
-        const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;  // real-sample index of staged element 0
-        float* pe = smem + L.stage[buf];
-        float* po = pe + a.stage_half;
-        for (int u = tid; u < len; u += kWarpsPerCta * 32) {
-            const int r = r0 + u;
-            const bool valid = r >= 0 && r < sd.n_valid;
-            cp_async4(((u & 1) ? po : pe) + (u >> 1), valid ? src + r : src, valid);
+        const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
+        const int shift = (int)(((sd.pcm_offset + r0) % 4 + 4) % 4);
+        const int n_chunks = (len + shift + 3) >> 2;
+        for (int i = tid; i < n_chunks; i += kWarpsPerCta * 32) {
+            const int r = r0 - shift + 4 * i;
+            if (r >= 0 && r + 3 < sd.n_valid) {
+                cp_async16(raw + 4 * i, src + r, true);
+            } else if (r + 3 < 0 || r >= sd.n_valid) {
+                cp_async16(raw + 4 * i, src, false);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool valid = r + e >= 0 && r + e < sd.n_valid;
+                    cp_async4(raw + 4 * i + e, valid ? src + r + e : src, valid);
+                }
+            }
         }
         cp_async_commit();
     };
 
     long long q = blockIdx.x;
-    if (q < n_stages) issue_stage(q, 0);
-    for (int it = 0; q < n_stages; q += gridDim.x, ++it) {
-        const int buf = it & 1;
+    if (q < n_stages) issue_stage(q);
+    for (; q < n_stages; q += gridDim.x) {
         const long long seg = q / a.stages_per_seg;
         const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         const int len = (nfs - 1) * a.hop + kNfft;
-        float* se = smem + L.stage[buf];
-        float* so = se + a.stage_half;
 
         cp_async_wait_all();
-        __syncthreads();                       // stage q has landed; everyone is done with stage q-G
-        if (q + gridDim.x < n_stages) issue_stage(q + gridDim.x, buf ^ 1);
-
-        if (a.normalize) {                     // normalize_data in place, exact float32 op order
-            const float2 st = a.segstat[seg];
-            const float mn = st.x, range = __fsub_rn(st.y, st.x), rcp = __frcp_rn(range);
-            const bool fast_div = range > 1e-30f && range < 1e30f;
+        __syncthreads();                       // raw has stage q; every warp is done with the previous stage
+        {   // raw -> normalised even/odd planes (normalize_data, exact float32 op order)
+            const cac_segment sd = a.segs[seg];
+            const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
+            const int shift = (int)(((sd.pcm_offset + r0) % 4 + 4) % 4);
+            const int n_chunks = (len + shift + 3) >> 2;
             const int s0 = f0 * a.hop - kNfft / 2;            // segment sample index of staged element 0
-            const int ulo = max(0, -s0), uhi = min(len, a.seg_len - s0);   // librosa's centre padding stays 0
-            for (int u = ulo + tid; u < uhi; u += kWarpsPerCta * 32) {
-                float* p = ((u & 1) ? so : se) + (u >> 1);
-                float x = __fsub_rn(*p, mn);
-                x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
-                x = __fadd_rn(x, 0.000001f);
-                *p = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
+            float mn = 0.f, range = 1.f, rcp = 1.f;
+            if (a.normalize) {
+                const float2 st = a.segstat[seg];
+                mn = st.x; range = __fsub_rn(st.y, st.x); rcp = __frcp_rn(range);
             }
-            __syncthreads();
+            const bool fast_div = range > 1e-30f && range < 1e30f;
+            for (int i = tid; i < n_chunks; i += kWarpsPerCta * 32) {
+                const float4 v4 = reinterpret_cast<const float4*>(raw)[i];
+                const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int u = 4 * i + e - shift;
+                    const int sidx = s0 + u;
+                    float x = v[e];
+                    if (a.normalize) {
+                        x = __fsub_rn(x, mn);
+                        x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
+                        x = __fadd_rn(x, 0.000001f);
+                        x = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
+                    }
+                    if (sidx < 0 || sidx >= a.seg_len) x = 0.f;   // librosa's centre padding stays zero
+                    if (u >= 0 && u < len) ((u & 1) ? so : se)[u >> 1] = x;
+                }
+            }
         }
+        __syncthreads();                       // planes ready; raw is free again
+        if (q + gridDim.x < n_stages) issue_stage(q + gridDim.x);
 
         float vmax = 0.f;
         float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
@@ -338,8 +371,18 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 const float* pp = pbuf + (live ? bstart[m] : 0);
                 const int gm = gmax[g];
                 float acc = 0.f;
-                for (int i = 0; i < gm; ++i)
-                    if (i < len_m) acc = fmaf(w[i], pp[i], acc);
+                for (int i = 0; i < gm; i += 4) {           // same ascending tap order as a plain loop
+                    float wv[4], pv[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const bool on = i + e < len_m;
+                        wv[e] = on ? w[i + e] : 0.f;
+                        pv[e] = on ? pp[i + e] : 0.f;
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (i + e < len_m) acc = fmaf(wv[e], pv[e], acc);
+                }
                 if (live) {
                     outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
                     vmax = fmaxf(vmax, acc);
