@@ -46,6 +46,12 @@ struct cac_plan {
     std::vector<float> weights;
     int kmin, kmax;
     int frames_per_stage, stage_half;
+    // fused-kernel filterbank (see FeatArgs): padded tap-major weights + band starts, host and device copies
+    std::vector<float> wpad;
+    std::vector<int> mstart;
+    int n_groups = 0, pbuf_len = 0, gmax[16] = {0}, goff[16] = {0};
+    float* d_wpad = nullptr;
+    int* d_mstart = nullptr;
     std::string fused_unsupported;   // why cac_features_run cannot serve these parameters ("" = it can)
     // buffers owned by the *_host entry points
     float* d_pcm = nullptr;      size_t pcm_cap = 0;
@@ -112,6 +118,26 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     else if (kmax >= 1024) plan->fused_unsupported = "fused STFT->mel kernel covers FFT bins < 1024 (fmax < sr/4)";
     plan->kmin = kmin;
     plan->kmax = kmax;
+    // padded tap-major filterbank for the fused kernel
+    plan->n_groups = (p.n_mels + 31) / 32;
+    if (plan->n_groups > 16) plan->fused_unsupported = "fused kernel supports n_mels <= 512";
+    plan->mstart.assign(p.n_mels, 0);
+    int need = kmax - kmin + 1;
+    for (int g = 0; g < plan->n_groups && g < 16; ++g) {
+        int gm = 0;
+        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) gm = plan->bt.len[m] > gm ? plan->bt.len[m] : gm;
+        gm = (gm + 3) / 4 * 4;
+        plan->gmax[g] = gm;
+        plan->goff[g] = (int)plan->wpad.size();
+        plan->wpad.resize(plan->wpad.size() + (size_t)gm * 32, 0.0f);
+        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) {
+            plan->mstart[m] = plan->bt.start[m] - kmin;
+            for (int t = 0; t < plan->bt.len[m]; ++t)
+                plan->wpad[plan->goff[g] + (size_t)t * 32 + (m - g * 32)] = plan->weights[plan->bt.off[m] + t];
+            if (plan->mstart[m] + gm > need) need = plan->mstart[m] + gm;
+        }
+    }
+    plan->pbuf_len = (need + 31) / 32 * 32;
     // frames staged per round: a multiple of the 12 warps per CTA when it fits the 227 KB of shared
     // memory (hop 281 -> 12), else the largest smaller count (some warps then idle during the FFTs)
     plan->frames_per_stage = 0;
@@ -122,12 +148,27 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
         FeatArgs a{};
         a.stage_half = half;
         a.nbins = kmax - kmin + 1;
-        a.n_taps = (int)plan->weights.size();
+        a.n_taps = (int)plan->wpad.size();
+        a.pbuf_len = plan->pbuf_len;
         a.n_mels = p.n_mels;
         if (feat_smem_bytes(a) <= 227 * 1024) { plan->frames_per_stage = fs; plan->stage_half = half; break; }
     }
     if (!plan->frames_per_stage && plan->fused_unsupported.empty())
         plan->fused_unsupported = "parameters exceed the shared-memory budget of the fused kernel";
+    if (plan->fused_unsupported.empty()) {
+        cudaSetDevice(device);
+        cudaError_t e1 = cudaMalloc((void**)&plan->d_wpad, plan->wpad.size() * sizeof(float) + 16);
+        cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, plan->mstart.size() * sizeof(int) + 16);
+        if (e1 == cudaSuccess && e2 == cudaSuccess) {
+            e1 = cudaMemcpy(plan->d_wpad, plan->wpad.data(), plan->wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
+            e2 = cudaMemcpy(plan->d_mstart, plan->mstart.data(), plan->mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
+        }
+        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+            cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
+            delete plan;
+            return fail(CAC_ERR_ALLOC, "could not upload the filterbank tables");
+        }
+    }
     *out = plan;
     return CAC_OK;
 }
@@ -136,6 +177,7 @@ extern "C" int cac_plan_destroy(cac_plan* plan) {
     if (!plan) return CAC_OK;
     cudaSetDevice(plan->device);
     if (plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
+    cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
     cudaFree(plan->d_pcm); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
     delete plan;
@@ -194,7 +236,12 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     a.nbins = plan->kmax - plan->kmin + 1;
     a.frames_per_stage = plan->frames_per_stage;
     a.stages_per_seg = (plan->n_frames + plan->frames_per_stage - 1) / plan->frames_per_stage;
-    a.n_taps = (int)plan->weights.size();
+    a.n_taps = (int)plan->wpad.size();
+    a.wpad = plan->d_wpad;
+    a.mstart = plan->d_mstart;
+    a.n_groups = plan->n_groups;
+    a.pbuf_len = plan->pbuf_len;
+    for (int g = 0; g < 16; ++g) { a.gmax[g] = plan->gmax[g]; a.goff[g] = plan->goff[g]; }
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
     CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));

@@ -32,7 +32,16 @@ struct FeatArgs {
     int nbins;             // kmax - kmin + 1
     int stages_per_seg;    // ceil(n_frames / frames_per_stage)
     int frames_per_stage;  // multiple of 8: frames staged (and transformed) per round
-    int n_taps;            // packed filterbank weights
+    int n_taps;            // floats in wpad
+    // Filterbank for the fused kernel: mel rows in groups of 32 (lane = row within the group), every
+    // row of a group zero-padded to the group's longest band (multiple of 4), stored tap-major
+    // wpad[goff[g] + t*32 + lane] so that a warp reads it conflict-free and without predicates.
+    const float* wpad;
+    const int* mstart;     // [n_mels] first bin of the band minus kmin
+    int n_groups;
+    int pbuf_len;          // floats per warp power-spectrum buffer (covers the padded reads)
+    int gmax[16];          // padded band length of group g
+    int goff[16];          // offset of group g inside wpad
     int stage_half;        // floats reserved for each of the even/odd sample planes
     int normalize;
 };

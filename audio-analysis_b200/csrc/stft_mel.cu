@@ -18,7 +18,7 @@ __constant__ float c_weights[kMaxTaps];
 
 constexpr int kNfft = 4096;
 constexpr int kExStride = 33;                 // floats per exchange row (odd -> conflict-free transpose)
-constexpr int kExFloats = 64 * kExStride;     // one plane (re or im) of one warp's exchange buffer
+constexpr int kExFloats = 2 * 32 * kExStride; // one warp's exchange buffer: 32 rows x 33 float2
 constexpr int kWarpsPerCta = 12;               // 12 warps x 168 registers fill the register file
 constexpr int kTileFrames = 32;
 constexpr int kPStride = 33;                  // floats per power-spectrum row (bin): odd -> conflict-free both ways
@@ -42,19 +42,22 @@ struct WinLoad {
 };
 
 // ---- transpose through shared memory: row k1 (pass-1 output index), column n2 (= lane) -----
-template <int K1>
+// The buffer holds 32 rows of 33 float2 (re, im); rows k1 = 0..31 go through first, then rows 32..63,
+// so each transfer is a 64-bit shared-memory access (half the instructions of separate re/im planes).
+template <int K1, int BASE>
 struct ExWrite {
-    static __device__ __forceinline__ void run(const float (&v)[64], float* ex_lane) {
-        ex_lane[K1 * kExStride] = v[out_pos(64, K1)];
-        if constexpr (K1 + 1 < 64) ExWrite<K1 + 1>::run(v, ex_lane);
+    static __device__ __forceinline__ void run(const float (&vr)[64], const float (&vi)[64], float2* ex_lane) {
+        ex_lane[K1 * kExStride] = make_float2(vr[out_pos(64, BASE + K1)], vi[out_pos(64, BASE + K1)]);
+        if constexpr (K1 + 1 < 32) ExWrite<K1 + 1, BASE>::run(vr, vi, ex_lane);
     }
 };
 template <int N2>
 struct ExRead {
-    static __device__ __forceinline__ void run(float (&v0)[32], float (&v1)[32], const float* ex_row) {
-        v0[N2] = ex_row[N2];
-        v1[N2] = ex_row[32 * kExStride + N2];
-        if constexpr (N2 + 1 < 32) ExRead<N2 + 1>::run(v0, v1, ex_row);
+    static __device__ __forceinline__ void run(float (&vr)[32], float (&vi)[32], const float2* ex_row) {
+        const float2 t = ex_row[N2];
+        vr[N2] = t.x;
+        vi[N2] = t.y;
+        if constexpr (N2 + 1 < 32) ExRead<N2 + 1>::run(vr, vi, ex_row);
     }
 };
 
@@ -155,14 +158,15 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     fft_dif<64>(ar, ai);
 
     float z0r[32], z0i[32], z1r[32], z1i[32];
+    float2* ex2 = reinterpret_cast<float2*>(ex);
     __syncwarp();
-    ExWrite<0>::run(ar, ex + lane);
+    ExWrite<0, 0>::run(ar, ai, ex2 + lane);
     __syncwarp();
-    ExRead<0>::run(z0r, z1r, ex + lane * kExStride);
+    ExRead<0>::run(z0r, z0i, ex2 + lane * kExStride);
     __syncwarp();
-    ExWrite<0>::run(ai, ex + lane);
+    ExWrite<0, 32>::run(ar, ai, ex2 + lane);
     __syncwarp();
-    ExRead<0>::run(z0i, z1i, ex + lane * kExStride);
+    ExRead<0>::run(z1r, z1i, ex2 + lane * kExStride);
 
     {
         Twid tw;
@@ -206,23 +210,21 @@ struct FeatSmem {
     int raw;           // raw samples of the next stage as fetched by cp.async (stage_len + 8 floats)
     int stage;         // 2 planes (even / odd samples) of stage_half floats: normalised samples of this stage
     int ex;            // 8 warps x kExFloats
-    int pbuf;          // 8 warps x nbins_pad
-    int nbins_pad;
-    int wts;           // packed band weights
-    int bands;         // int: start[n_mels], len[n_mels], off[n_mels], gmax[(n_mels+31)/32]
+    int pbuf;          // warps x pbuf_len
+    int wts;           // padded tap-major band weights (FeatArgs::wpad)
+    int bands;         // int: mstart[n_mels]
     int ltab;          // 32 x 32
     int total;
 };
-__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int nbins, int n_taps, int n_mels) {
+__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int pbuf_len, int n_taps, int n_mels) {
     FeatSmem L;
     int o = 0;
     L.raw = o; o += 2 * stage_half;
     L.stage = o; o += 2 * stage_half;
     L.ex = o; o += kWarpsPerCta * kExFloats;
-    L.nbins_pad = (nbins + 31) / 32 * 32;
-    L.pbuf = o; o += kWarpsPerCta * L.nbins_pad;
+    L.pbuf = o; o += kWarpsPerCta * pbuf_len;
     L.wts = o; o += (n_taps + 3) / 4 * 4;
-    L.bands = o; o += 3 * n_mels + (n_mels + 31) / 32;
+    L.bands = o; o += n_mels;
     o = (o + 31) / 32 * 32;
     L.ltab = o; o += 32 * 32;
     L.total = o;
@@ -236,30 +238,18 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int nbins, 
 template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
-    const FeatSmem L = feat_smem_layout(a.stage_half, a.nbins, a.n_taps, a.n_mels);
+    const FeatSmem L = feat_smem_layout(a.stage_half, a.pbuf_len, a.n_taps, a.n_mels);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* ex = smem + L.ex + warp * kExFloats;
-    float* pbuf = smem + L.pbuf + warp * L.nbins_pad;
+    float* pbuf = smem + L.pbuf + warp * a.pbuf_len;
     float* wts = smem + L.wts;
-    int* bstart = reinterpret_cast<int*>(smem + L.bands);
-    int* blen = bstart + a.n_mels;
-    int* boff = blen + a.n_mels;
-    int* gmax = boff + a.n_mels;
+    int* mstart = reinterpret_cast<int*>(smem + L.bands);
     float* ltab = smem + L.ltab;
-    const int n_groups = (a.n_mels + 31) / 32;
 
     // ---- one-time tables ------------------------------------------------------------------------
-    for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = c_weights[i];
-    for (int m = tid; m < a.n_mels; m += kWarpsPerCta * 32) {
-        bstart[m] = c_bands.start[m] - a.kmin;
-        blen[m] = c_bands.len[m];
-        boff[m] = c_bands.off[m];
-    }
-    if (tid < n_groups) {
-        int g = 0;
-        for (int m = tid * 32; m < min(a.n_mels, tid * 32 + 32); ++m) g = max(g, (int)c_bands.len[m]);
-        gmax[tid] = g;
-    }
+    for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
+    for (int m = tid; m < a.n_mels; m += kWarpsPerCta * 32) mstart[m] = a.mstart[m];
+    for (int i = lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;   // the zero-weight taps read finite values
     if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
@@ -332,23 +322,38 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 const float2 st = a.segstat[seg];
                 mn = st.x; range = __fsub_rn(st.y, st.x); rcp = __frcp_rn(range);
             }
-            const bool fast_div = range > 1e-30f && range < 1e30f;
+            const bool fast_div = a.normalize && range > 1e-30f && range < 1e30f;
+            const float4* raw4 = reinterpret_cast<const float4*>(raw);
+            // element e of chunk i is staged element u = 4i + e - shift; even u -> se[u/2], odd u -> so[u/2]
+            float* pa = (shift & 1) ? so : se;               // plane of elements e = 0, 2
+            float* pb = (shift & 1) ? se : so;               // plane of elements e = 1, 3
             for (int i = tid; i < n_chunks; i += kWarpsPerCta * 32) {
-                const float4 v4 = reinterpret_cast<const float4*>(raw)[i];
-                const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+                const float4 v4 = raw4[i];
+                const int ub = 4 * i - shift;
+                const int sb = s0 + ub;
+                float v[4] = {v4.x, v4.y, v4.z, v4.w};
+                if (fast_div && ub >= 0 && ub + 3 < len && sb >= 0 && sb + 3 < a.seg_len) {
+                    // interior chunk: no bounds to honour, correctly rounded division via the reciprocal
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int u = 4 * i + e - shift;
-                    const int sidx = s0 + u;
-                    float x = v[e];
-                    if (a.normalize) {
-                        x = __fsub_rn(x, mn);
-                        x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
-                        x = __fadd_rn(x, 0.000001f);
-                        x = __fmul_rn(__fsub_rn(x, 0.5f), 2.0f);
+                    for (int e = 0; e < 4; ++e) {
+                        float x = div_by(__fsub_rn(v[e], mn), range, rcp);
+                        v[e] = __fmul_rn(__fsub_rn(__fadd_rn(x, 0.000001f), 0.5f), 2.0f);
                     }
-                    if (sidx < 0 || sidx >= a.seg_len) x = 0.f;   // librosa's centre padding stays zero
-                    if (u >= 0 && u < len) ((u & 1) ? so : se)[u >> 1] = x;
+                    const int ia = ub >> 1, ib = (ub + 1) >> 1;
+                    pa[ia] = v[0]; pb[ib] = v[1]; pa[ia + 1] = v[2]; pb[ib + 1] = v[3];
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int u = ub + e, sidx = sb + e;
+                        float x = v[e];
+                        if (a.normalize) {
+                            x = __fsub_rn(x, mn);
+                            x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
+                            x = __fmul_rn(__fsub_rn(__fadd_rn(x, 0.000001f), 0.5f), 2.0f);
+                        }
+                        if (sidx < 0 || sidx >= a.seg_len) x = 0.f;   // librosa's centre padding stays zero
+                        if (u >= 0 && u < len) ((u & 1) ? so : se)[u >> 1] = x;
+                    }
                 }
             }
         }
@@ -363,25 +368,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             __syncwarp();
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
 #pragma unroll 1
-            for (int g = 0; g < n_groups; ++g) {
+            for (int g = 0; g < a.n_groups; ++g) {
                 const int m = g * 32 + lane;
                 const bool live = m < a.n_mels;
-                const int len_m = live ? blen[m] : 0;
-                const float* w = wts + (live ? boff[m] : 0);
-                const float* pp = pbuf + (live ? bstart[m] : 0);
-                const int gm = gmax[g];
+                const float* pp = pbuf + (live ? mstart[m] : 0);
+                const float* wg = wts + a.goff[g] + lane;
+                const int gm = a.gmax[g];
                 float acc = 0.f;
-                for (int i = 0; i < gm; i += 4) {           // same ascending tap order as a plain loop
-                    float wv[4], pv[4];
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const bool on = i + e < len_m;
-                        wv[e] = on ? w[i + e] : 0.f;
-                        pv[e] = on ? pp[i + e] : 0.f;
-                    }
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (i + e < len_m) acc = fmaf(wv[e], pv[e], acc);
+                for (int i = 0; i < gm; i += 4) {           // ascending taps; the padding taps add +0
+                    const float w0 = wg[i * 32], w1 = wg[(i + 1) * 32], w2 = wg[(i + 2) * 32], w3 = wg[(i + 3) * 32];
+                    const float p0 = pp[i], p1 = pp[i + 1], p2 = pp[i + 2], p3 = pp[i + 3];
+                    acc = fmaf(w0, p0, acc);
+                    acc = fmaf(w1, p1, acc);
+                    acc = fmaf(w2, p2, acc);
+                    acc = fmaf(w3, p3, acc);
                 }
                 if (live) {
                     outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
@@ -504,7 +504,7 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.nbins, a.n_taps, a.n_mels).total;
+    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.pbuf_len, a.n_taps, a.n_mels).total;
 }
 
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
