@@ -125,19 +125,28 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     int need = kmax - kmin + 1;
     for (int g = 0; g < plan->n_groups && g < 16; ++g) {
         int gm = 0;
-        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) gm = plan->bt.len[m] > gm ? plan->bt.len[m] : gm;
+        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) {
+            int front = (plan->bt.start[m] - kmin) & 3;
+            gm = plan->bt.len[m] + front > gm ? plan->bt.len[m] + front : gm;
+        }
         gm = (gm + 3) / 4 * 4;
         plan->gmax[g] = gm;
         plan->goff[g] = (int)plan->wpad.size();
         plan->wpad.resize(plan->wpad.size() + (size_t)gm * 32, 0.0f);
         for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) {
-            plan->mstart[m] = plan->bt.start[m] - kmin;
-            for (int t = 0; t < plan->bt.len[m]; ++t)
-                plan->wpad[plan->goff[g] + (size_t)t * 32 + (m - g * 32)] = plan->weights[plan->bt.off[m] + t];
+            const int s0 = plan->bt.start[m] - kmin, front = s0 & 3, lane = m - g * 32;
+            plan->mstart[m] = s0 - front;
+            for (int t = 0; t < plan->bt.len[m]; ++t) {
+                const int tt = t + front;
+                plan->wpad[plan->goff[g] + ((size_t)(tt >> 2) * 32 + lane) * 4 + (tt & 3)] =
+                    plan->weights[plan->bt.off[m] + t];
+            }
             if (plan->mstart[m] + gm > need) need = plan->mstart[m] + gm;
         }
     }
     plan->pbuf_len = (need + 31) / 32 * 32;
+    if (plan->pbuf_len > 2 * 32 * 33 && plan->fused_unsupported.empty())
+        plan->fused_unsupported = "band range exceeds the per-warp power-spectrum buffer of the fused kernel";
     // frames staged per round: a multiple of the 12 warps per CTA when it fits the 227 KB of shared
     // memory (hop 281 -> 12), else the largest smaller count (some warps then idle during the FFTs)
     plan->frames_per_stage = 0;

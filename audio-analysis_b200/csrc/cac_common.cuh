@@ -34,10 +34,11 @@ struct FeatArgs {
     int frames_per_stage;  // multiple of 8: frames staged (and transformed) per round
     int n_taps;            // floats in wpad
     // Filterbank for the fused kernel: mel rows in groups of 32 (lane = row within the group), every
-    // row of a group zero-padded to the group's longest band (multiple of 4), stored tap-major
-    // wpad[goff[g] + t*32 + lane] so that a warp reads it conflict-free and without predicates.
+    // band starts at a multiple of 4 bins (zero weights in front) and is zero-padded to the group's
+    // longest band (multiple of 4); stored as float4 per (tap quad, lane):
+    // wpad[goff[g] + ((t/4)*32 + lane)*4 + t%4] -> conflict-free 128-bit reads without predicates.
     const float* wpad;
-    const int* mstart;     // [n_mels] first bin of the band minus kmin
+    const int* mstart;     // [n_mels] (first bin of the band minus kmin) rounded down to a multiple of 4
     int n_groups;
     int pbuf_len;          // floats per warp power-spectrum buffer (covers the padded reads)
     int gmax[16];          // padded band length of group g

@@ -167,6 +167,7 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     ExWrite<0, 32>::run(ar, ai, ex2 + lane);
     __syncwarp();
     ExRead<0>::run(z1r, z1i, ex2 + lane * kExStride);
+    __syncwarp();   // pbuf aliases ex: nobody may still be reading the exchange rows when the power values land
 
     {
         Twid tw;
@@ -210,19 +211,17 @@ struct FeatSmem {
     int raw;           // raw samples of the next stage as fetched by cp.async (stage_len + 8 floats)
     int stage;         // 2 planes (even / odd samples) of stage_half floats: normalised samples of this stage
     int ex;            // 8 warps x kExFloats
-    int pbuf;          // warps x pbuf_len
     int wts;           // padded tap-major band weights (FeatArgs::wpad)
     int bands;         // int: mstart[n_mels]
     int ltab;          // 32 x 32
     int total;
 };
-__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int pbuf_len, int n_taps, int n_mels) {
+__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps, int n_mels) {
     FeatSmem L;
     int o = 0;
     L.raw = o; o += 2 * stage_half;
     L.stage = o; o += 2 * stage_half;
     L.ex = o; o += kWarpsPerCta * kExFloats;
-    L.pbuf = o; o += kWarpsPerCta * pbuf_len;
     L.wts = o; o += (n_taps + 3) / 4 * 4;
     L.bands = o; o += n_mels;
     o = (o + 31) / 32 * 32;
@@ -238,10 +237,10 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int pbuf_le
 template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
-    const FeatSmem L = feat_smem_layout(a.stage_half, a.pbuf_len, a.n_taps, a.n_mels);
+    const FeatSmem L = feat_smem_layout(a.stage_half, a.n_taps, a.n_mels);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* ex = smem + L.ex + warp * kExFloats;
-    float* pbuf = smem + L.pbuf + warp * a.pbuf_len;
+    float* pbuf = ex;   // the power spectrum reuses the warp's exchange buffer once pass 2 has read it
     float* wts = smem + L.wts;
     int* mstart = reinterpret_cast<int*>(smem + L.bands);
     float* ltab = smem + L.ltab;
@@ -249,7 +248,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     // ---- one-time tables ------------------------------------------------------------------------
     for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
     for (int m = tid; m < a.n_mels; m += kWarpsPerCta * 32) mstart[m] = a.mstart[m];
-    for (int i = lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;   // the zero-weight taps read finite values
     if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
@@ -365,23 +363,25 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
 #pragma unroll 1
         for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
             fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt, a.kmin, a.nbins);
+            for (int i = a.nbins + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;   // zero-weight taps read zeros
             __syncwarp();
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
 #pragma unroll 1
             for (int g = 0; g < a.n_groups; ++g) {
                 const int m = g * 32 + lane;
                 const bool live = m < a.n_mels;
-                const float* pp = pbuf + (live ? mstart[m] : 0);
-                const float* wg = wts + a.goff[g] + lane;
-                const int gm = a.gmax[g];
+                // band start rounded down to 4 bins (zero weights in front): both loads are 128-bit
+                const float4* pp = reinterpret_cast<const float4*>(pbuf + (live ? mstart[m] : 0));
+                const float4* wg = reinterpret_cast<const float4*>(wts + a.goff[g]) + lane;
+                const int gm4 = a.gmax[g] >> 2;
                 float acc = 0.f;
-                for (int i = 0; i < gm; i += 4) {           // ascending taps; the padding taps add +0
-                    const float w0 = wg[i * 32], w1 = wg[(i + 1) * 32], w2 = wg[(i + 2) * 32], w3 = wg[(i + 3) * 32];
-                    const float p0 = pp[i], p1 = pp[i + 1], p2 = pp[i + 2], p3 = pp[i + 3];
-                    acc = fmaf(w0, p0, acc);
-                    acc = fmaf(w1, p1, acc);
-                    acc = fmaf(w2, p2, acc);
-                    acc = fmaf(w3, p3, acc);
+                for (int i = 0; i < gm4; ++i) {             // ascending taps; the padding taps add +0
+                    const float4 w = wg[i * 32];
+                    const float4 p = pp[i];
+                    acc = fmaf(w.x, p.x, acc);
+                    acc = fmaf(w.y, p.y, acc);
+                    acc = fmaf(w.z, p.z, acc);
+                    acc = fmaf(w.w, p.w, acc);
                 }
                 if (live) {
                     outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
@@ -504,7 +504,7 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.pbuf_len, a.n_taps, a.n_mels).total;
+    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.n_taps, a.n_mels).total;
 }
 
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
