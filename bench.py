@@ -159,6 +159,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -237,14 +238,16 @@ def main():
         for _ in range(n_chunks):
             plan.run_host(pool_np, seg_chunk, out_host)
 
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 3))
-    for _ in range(e2e_steps):
+    e2e_s = float("nan")
+    if not args.no_e2e:
         e2e_step()
-    barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(1, min(args.steps, 3))
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
 
     # ---- reduce over ranks (max time) -------------------------------------------------------------------
     t = torch.tensor([total_ms, e2e_s, float(np.median(kernel_ms))], dtype=torch.float64, device=dev)
