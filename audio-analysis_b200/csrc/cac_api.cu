@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "api_util.h"
 #include "cac_common.cuh"
 
 namespace cac {
@@ -26,16 +27,10 @@ static thread_local std::string g_err;
 static std::atomic<uint64_t> g_next_plan_id{1};
 static uint64_t g_const_owner[64] = {0};   // plan whose band table is in __constant__ memory, per device
 
-static int fail(int code, const std::string& msg) {
+int cac::fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
 }
-#define CUDA_TRY(expr)                                                                         \
-    do {                                                                                       \
-        cudaError_t _e = (expr);                                                               \
-        if (_e != cudaSuccess)                                                                 \
-            return fail(CAC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));     \
-    } while (0)
 
 struct cac_plan {
     cac_params p;
@@ -254,17 +249,6 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
     CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));
-    return CAC_OK;
-}
-
-template <class T>
-static int ensure_cap(T** ptr, size_t* cap, size_t bytes) {
-    if (bytes <= *cap) return CAC_OK;
-    if (*ptr) cudaFree(*ptr);
-    *ptr = nullptr; *cap = 0;
-    cudaError_t e = cudaMalloc((void**)ptr, bytes);
-    if (e != cudaSuccess) return fail(CAC_ERR_ALLOC, std::string("cudaMalloc: ") + cudaGetErrorString(e));
-    *cap = bytes;
     return CAC_OK;
 }
 

@@ -50,7 +50,17 @@ lib.cac_normalize_run.argtypes = [_vp, _vp, _i64, _i32, _vp]
 lib.cac_mel_project_run.argtypes = [_vp, _vp, _i32, _vp, _vp]
 lib.cac_power_to_db_run.argtypes = [_vp, _vp, _i64, _i64, _vp, _vp]
 
-EXPORTS = ["cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
+lib.cac_ci_plan_create.argtypes = [_i32, _vp, _vp, ctypes.c_int, ctypes.POINTER(_vp)]
+lib.cac_ci_plan_destroy.argtypes = [_vp]
+lib.cac_ci_window_count.argtypes = [_i64]
+lib.cac_ci_window_count.restype = _i64
+lib.cac_ci_bins_run.argtypes = [_vp, _vp, _i64, _i32, _vp, _vp]
+lib.cac_ci_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
+lib.cac_ci_host.argtypes = [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp]
+lib.cac_ci_entries_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
+
+EXPORTS = ["cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
+           "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
 
@@ -186,3 +196,88 @@ def power_to_db(x, device=0):
         check(lib.cac_power_to_db_run(t.data_ptr(), out.data_ptr(), n_items, t.numel() // n_items, work.data_ptr(),
                                       _stream_ptr(torch)))
     return out.cpu().numpy() if was_np else out
+
+
+class CiPlan:
+    """Old Cacophony Index plan (cac_ci_*): float64 DCT band energies, points and score order statistics."""
+
+    def __init__(self, edges, window, device=0):
+        edges = np.ascontiguousarray(edges, dtype=np.int32)
+        window = np.ascontiguousarray(window, dtype=np.float64)
+        assert edges.shape == (11,)
+        self.device = device
+        self._h = ctypes.c_void_p()
+        check(lib.cac_ci_plan_create(int(window.shape[0]), edges.ctypes.data_as(_vp), window.ctypes.data_as(_vp),
+                                     device, ctypes.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib.cac_ci_plan_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def window_count(n_samples):
+        return int(lib.cac_ci_window_count(int(n_samples)))
+
+    def bins(self, pcm, n_windows, hop):
+        """get_ci_bins on windows pcm[hop*w : hop*w + 2048] of a CUDA float32 tensor -> CUDA float64 [n, 10]."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        assert n_windows == 0 or hop * (n_windows - 1) + 2048 <= pcm.numel()
+        out = torch.empty((n_windows, 10), dtype=torch.float64, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_ci_bins_run(self._h, pcm.data_ptr(), n_windows, hop, out.data_ptr(), _stream_ptr(torch)))
+        return out
+
+    def run(self, pcm, item_offset, item_samples, want_points=True):
+        """calculate()'s loop on recordings stored in the flat CUDA tensor `pcm`; returns
+        (bins [W, 10] float64, points [W] uint8 or None, win_base [n_items + 1] int64 numpy)."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        off = np.ascontiguousarray(item_offset, dtype=np.int64)
+        ns = np.ascontiguousarray(item_samples, dtype=np.int64)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        assert off.shape == ns.shape and (off + ns <= pcm.numel()).all()
+        counts = np.array([self.window_count(v) for v in ns], dtype=np.int64)
+        base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+        total = int(base[-1])
+        bins = torch.empty((total, 10), dtype=torch.float64, device=dev)
+        points = torch.empty((total,), dtype=torch.uint8, device=dev) if want_points else None
+        with torch.cuda.device(dev):
+            check(lib.cac_ci_run(self._h, pcm.data_ptr(), off.ctypes.data_as(_vp), ns.ctypes.data_as(_vp), len(off),
+                                 bins.data_ptr(), points.data_ptr() if want_points else None, _stream_ptr(torch)))
+        return bins, points, base
+
+    def run_host(self, pcm, item_offset, item_samples):
+        pcm = np.ascontiguousarray(pcm, dtype=np.float32).reshape(-1)
+        off = np.ascontiguousarray(item_offset, dtype=np.int64)
+        ns = np.ascontiguousarray(item_samples, dtype=np.int64)
+        counts = np.array([self.window_count(v) for v in ns], dtype=np.int64)
+        base = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+        total = int(base[-1])
+        bins = np.empty((total, 10), dtype=np.float64)
+        points = np.empty((total,), dtype=np.uint8)
+        check(lib.cac_ci_host(self._h, pcm.ctypes.data_as(_vp), pcm.size, off.ctypes.data_as(_vp),
+                              ns.ctypes.data_as(_vp), len(off), bins.ctypes.data_as(_vp), points.ctypes.data_as(_vp)))
+        return bins, points, base
+
+    def entries(self, points, entry_start, entry_len):
+        """Order statistics of score_from_points for slices of the CUDA uint8 tensor `points`:
+        returns int32 numpy [n_entries, 2] = (sum of sorted[k0:k1], k1 - k0)."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        es = np.ascontiguousarray(entry_start, dtype=np.int64)
+        el = np.ascontiguousarray(entry_len, dtype=np.int32)
+        out = torch.empty((len(es), 2), dtype=torch.int32, device=dev)
+        if len(es):
+            with torch.cuda.device(dev):
+                check(lib.cac_ci_entries_run(self._h, points.data_ptr(), es.ctypes.data_as(_vp), el.ctypes.data_as(_vp),
+                                             len(es), out.data_ptr(), _stream_ptr(torch)))
+        return out.cpu().numpy()

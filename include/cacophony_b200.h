@@ -99,6 +99,42 @@ int cac_mel_project_run(cac_plan* plan, const float* d_mag, int32_t n_frames, fl
 int cac_power_to_db_run(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* d_work,
                         void* stream);
 
+/* ---- old Cacophony Index (src/cacophony_index.py) ------------------------------------------------
+ * float64 throughout, like the reference (numpy.hanning * window -> scipy.fftpack.dct -> band sums). */
+typedef struct cac_ci_plan cac_ci_plan;
+
+/* h_edges: the 11 band edges get_ci_bins derives from (window_size, sample_rate)
+ * (src/cacophony_index.py:58-63); h_window: numpy.hanning(window_size) (src/common.py:39-40).
+ * Only the layout calculate() uses (window 2048 at 16 kHz: edges 25..2048) is built; others fail. */
+int cac_ci_plan_create(int32_t window_size, const int32_t* h_edges, const double* h_window, int device,
+                       cac_ci_plan** out);
+int cac_ci_plan_destroy(cac_ci_plan* plan);
+/* len(range(1024, n_samples - 3072, 1024)): windows calculate()'s loop visits (src/cacophony_index.py:89-91). */
+int64_t cac_ci_window_count(int64_t n_samples);
+
+/* get_ci_bins (src/cacophony_index.py:53-66) on n_windows windows d_pcm[hop*w .. hop*w + 2048):
+ * d_bins[w][10] float64 band energies. */
+int cac_ci_bins_run(cac_ci_plan* plan, const float* d_pcm, int64_t n_windows, int32_t hop, double* d_bins,
+                    void* stream);
+
+/* calculate()'s hot loop (src/cacophony_index.py:86-97) for n_items recordings stored in d_pcm at
+ * h_item_offset[i] (h_item_samples[i] samples each, 16 kHz).  Windows are numbered globally,
+ * recording after recording (cac_ci_window_count each).  d_bins[window][10] = get_ci_bins;
+ * d_points[window] (may be NULL) = the reference's `points` entry for that window against the
+ * previous one, 255 for the first window of each recording (it only seeds previous_bins). */
+int cac_ci_run(cac_ci_plan* plan, const float* d_pcm, const int64_t* h_item_offset, const int64_t* h_item_samples,
+               int64_t n_items, double* d_bins, uint8_t* d_points, void* stream);
+/* Same through host buffers. */
+int cac_ci_host(cac_ci_plan* plan, const float* h_pcm, int64_t n_pcm, const int64_t* h_item_offset,
+                const int64_t* h_item_samples, int64_t n_items, double* h_bins, uint8_t* h_points);
+
+/* score_from_points' order statistics (src/cacophony_index.py:69-73) for n_entries slices
+ * d_points[h_entry_start[e] .. + h_entry_len[e]): d_out[e] = {sum(sorted[k0:k1]), k1 - k0} with
+ * k0 = int(len*0.75), k1 = int(len*0.95).  The float tail (mean, correction curve, rounding)
+ * stays with the caller. */
+int cac_ci_entries_run(cac_ci_plan* plan, const uint8_t* d_points, const int64_t* h_entry_start,
+                       const int32_t* h_entry_len, int64_t n_entries, int32_t* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

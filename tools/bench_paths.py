@@ -1,0 +1,78 @@
+#!/usr/bin/env python
+"""Device-resident timings of the secondary paths (BASELINE.json configs[2] and [3]); bench.py keeps the
+headline configs[1].  Prints one JSON line per path.  usage: python tools/bench_paths.py [ci] [morepork]"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from audio_analysis_b200 import synth  # noqa: E402
+
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+    os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+
+def timed(fn, warmup=3, steps=10):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def bench_ci(hours=8.0):
+    from audio_analysis_b200 import cacophony_index as C
+    pool = np.stack([synth.recording(900 + i, 60.0, 16000) for i in range(16)])
+    n_min = int(hours * 60)
+    reps = (n_min + len(pool) - 1) // len(pool)
+    pcm = torch.from_numpy(pool).cuda().repeat(reps, 1)[:n_min].contiguous().reshape(-1)
+    n = pcm.numel()
+    plan = C._plan(2048, 16000)
+    ms = timed(lambda: plan.run(pcm, [0], [n]))
+    t0 = time.perf_counter()
+    res = C.calculate_batch(pcm, [0], [n])[0]
+    wall = time.perf_counter() - t0
+    n_win = plan.window_count(n)
+    algo = n * 4 + n_win * (80 + 1)
+    print(json.dumps({"path": "cacophony_index (configs[3])", "recording_hours": hours, "samples": n, "windows": n_win,
+                      "entries": len(res["cacophony_index_old"]), "ms_bins_plus_points": ms,
+                      "recording_hours_per_s": hours / (ms * 1e-3), "algorithmic_GBps": algo / ms / 1e6,
+                      "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "calculate_batch_wall_ms": wall * 1e3,
+                      "dtype": "f64"}), flush=True)
+
+
+def bench_morepork(n_rec=4096):
+    from audio_analysis_b200 import identify_morepork as M
+    pool = np.stack([synth.recording(300 + i, 60.0, 48000) for i in range(16)])
+    n_rec = int(os.environ.get("CAC_MOREPORK_RECORDINGS", n_rec))
+    reps = (n_rec + len(pool) - 1) // len(pool)
+    pcm = torch.from_numpy(pool).cuda().repeat(reps, 1)[:n_rec].contiguous()
+    plan = M._plan(48000)
+    out = None
+
+    def step():
+        nonlocal out
+        out = plan.run(pcm, out=out)
+    ms = timed(step, steps=5)
+    algo = pcm.numel() * 4 + out[0].numel() * 4
+    print(json.dumps({"path": "identify_morepork (configs[2])", "recordings": n_rec, "ms": ms,
+                      "recording_hours_per_s": n_rec / 60.0 / (ms * 1e-3), "algorithmic_GBps": algo / ms / 1e6,
+                      "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "dtype": "f32"}), flush=True)
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["ci"]
+    if "ci" in which:
+        bench_ci()
+    if "morepork" in which:
+        bench_morepork()
