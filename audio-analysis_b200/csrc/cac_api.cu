@@ -9,6 +9,7 @@
 
 #include "api_util.h"
 #include "cac_common.cuh"
+#include "mel_bands.h"
 
 namespace cac {
 cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st);
@@ -37,14 +38,8 @@ struct cac_plan {
     int device;
     int n_frames;
     uint64_t id;
-    BandTable bt;
-    std::vector<float> weights;
-    int kmin, kmax;
+    MelBands mb;                     // banded filterbank (mel_bands.h), host copy
     int frames_per_stage, stage_half;
-    // fused-kernel filterbank (see FeatArgs): padded tap-major weights + band starts, host and device copies
-    std::vector<float> wpad;
-    std::vector<int> mstart;
-    int n_groups = 0, pbuf_len = 0, gmax[16] = {0}, goff[16] = {0};
     float* d_wpad = nullptr;
     int* d_mstart = nullptr;
     std::string fused_unsupported;   // why cac_features_run cannot serve these parameters ("" = it can)
@@ -69,7 +64,7 @@ extern "C" int cac_device_count(void) {
 
 static int ensure_constants(cac_plan* plan, cudaStream_t st) {
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) return CAC_OK;
-    CUDA_TRY(upload_bands(plan->bt, plan->weights.data(), (int)plan->weights.size(), st));
+    CUDA_TRY(upload_bands(plan->mb.bt, plan->mb.weights.data(), (int)plan->mb.weights.size(), st));
     if (plan->device < 64) g_const_owner[plan->device] = plan->id;
     return CAC_OK;
 }
@@ -93,54 +88,13 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     plan->id = g_next_plan_id++;
     plan->n_frames = 1 + p.segment_samples / p.hop_length;
     const int bins = 1 + p.n_fft / 2;
-    int kmin = bins, kmax = -1;
-    for (int m = 0; m < p.n_mels; ++m) {
-        int first = -1, last = -1;
-        for (int k = 0; k < bins; ++k)
-            if (w[(size_t)m * bins + k] != 0.0f) { if (first < 0) first = k; last = k; }
-        if (first < 0) { first = 0; last = -1; }          // empty filter: contributes zero
-        plan->bt.start[m] = (int16_t)first;
-        plan->bt.len[m] = (int16_t)(last - first + 1);
-        plan->bt.off[m] = (int32_t)plan->weights.size();
-        for (int k = first; k <= last; ++k) plan->weights.push_back(w[(size_t)m * bins + k]);
-        if (last >= first) { kmin = first < kmin ? first : kmin; kmax = last > kmax ? last : kmax; }
-    }
-    if (kmax < 0) { kmin = 0; kmax = 0; }
-    for (int m = 0; m < p.n_mels; ++m)
-        if (plan->bt.len[m] == 0) plan->bt.start[m] = (int16_t)kmin;
-    if ((int)plan->weights.size() > kMaxTaps) { delete plan; return fail(CAC_ERR_INVALID, "filterbank has too many taps"); }
+    const std::string berr = plan->mb.build(w, p.n_mels, bins);
+    if (!berr.empty()) { delete plan; return fail(CAC_ERR_INVALID, berr); }
+    const int kmin = plan->mb.kmin, kmax = plan->mb.kmax;
     if (p.n_fft != 4096) plan->fused_unsupported = "fused STFT->mel kernel supports n_fft == 4096 only";
     else if (kmax >= 1024) plan->fused_unsupported = "fused STFT->mel kernel covers FFT bins < 1024 (fmax < sr/4)";
-    plan->kmin = kmin;
-    plan->kmax = kmax;
-    // padded tap-major filterbank for the fused kernel
-    plan->n_groups = (p.n_mels + 31) / 32;
-    if (plan->n_groups > 16) plan->fused_unsupported = "fused kernel supports n_mels <= 512";
-    plan->mstart.assign(p.n_mels, 0);
-    int need = kmax - kmin + 1;
-    for (int g = 0; g < plan->n_groups && g < 16; ++g) {
-        int gm = 0;
-        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) {
-            int front = (plan->bt.start[m] - kmin) & 3;
-            gm = plan->bt.len[m] + front > gm ? plan->bt.len[m] + front : gm;
-        }
-        gm = (gm + 3) / 4 * 4;
-        plan->gmax[g] = gm;
-        plan->goff[g] = (int)plan->wpad.size();
-        plan->wpad.resize(plan->wpad.size() + (size_t)gm * 32, 0.0f);
-        for (int m = g * 32; m < p.n_mels && m < g * 32 + 32; ++m) {
-            const int s0 = plan->bt.start[m] - kmin, front = s0 & 3, lane = m - g * 32;
-            plan->mstart[m] = s0 - front;
-            for (int t = 0; t < plan->bt.len[m]; ++t) {
-                const int tt = t + front;
-                plan->wpad[plan->goff[g] + ((size_t)(tt >> 2) * 32 + lane) * 4 + (tt & 3)] =
-                    plan->weights[plan->bt.off[m] + t];
-            }
-            if (plan->mstart[m] + gm > need) need = plan->mstart[m] + gm;
-        }
-    }
-    plan->pbuf_len = (need + 31) / 32 * 32;
-    if (plan->pbuf_len > 2 * 32 * 33 && plan->fused_unsupported.empty())
+    if (plan->mb.n_groups > 16) plan->fused_unsupported = "fused kernel supports n_mels <= 512";
+    if (plan->mb.pbuf_len > 2 * 32 * 33 && plan->fused_unsupported.empty())
         plan->fused_unsupported = "band range exceeds the per-warp power-spectrum buffer of the fused kernel";
     // frames staged per round: a multiple of the 12 warps per CTA when it fits the 227 KB of shared
     // memory (hop 281 -> 12), else the largest smaller count (some warps then idle during the FFTs)
@@ -152,8 +106,8 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
         FeatArgs a{};
         a.stage_half = half;
         a.nbins = kmax - kmin + 1;
-        a.n_taps = (int)plan->wpad.size();
-        a.pbuf_len = plan->pbuf_len;
+        a.n_taps = (int)plan->mb.wpad.size();
+        a.pbuf_len = plan->mb.pbuf_len;
         a.n_mels = p.n_mels;
         if (feat_smem_bytes(a) <= 227 * 1024) { plan->frames_per_stage = fs; plan->stage_half = half; break; }
     }
@@ -161,11 +115,11 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
         plan->fused_unsupported = "parameters exceed the shared-memory budget of the fused kernel";
     if (plan->fused_unsupported.empty()) {
         cudaSetDevice(device);
-        cudaError_t e1 = cudaMalloc((void**)&plan->d_wpad, plan->wpad.size() * sizeof(float) + 16);
-        cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, plan->mstart.size() * sizeof(int) + 16);
+        cudaError_t e1 = cudaMalloc((void**)&plan->d_wpad, plan->mb.wpad.size() * sizeof(float) + 16);
+        cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, plan->mb.mstart.size() * sizeof(int) + 16);
         if (e1 == cudaSuccess && e2 == cudaSuccess) {
-            e1 = cudaMemcpy(plan->d_wpad, plan->wpad.data(), plan->wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
-            e2 = cudaMemcpy(plan->d_mstart, plan->mstart.data(), plan->mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
+            e1 = cudaMemcpy(plan->d_wpad, plan->mb.wpad.data(), plan->mb.wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
+            e2 = cudaMemcpy(plan->d_mstart, plan->mb.mstart.data(), plan->mb.mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
         }
         if (e1 != cudaSuccess || e2 != cudaSuccess) {
             cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
@@ -236,16 +190,16 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     a.hop = plan->p.hop_length;
     a.n_frames = plan->n_frames;
     a.n_mels = plan->p.n_mels;
-    a.kmin = plan->kmin;
-    a.nbins = plan->kmax - plan->kmin + 1;
+    a.kmin = plan->mb.kmin;
+    a.nbins = plan->mb.kmax - plan->mb.kmin + 1;
     a.frames_per_stage = plan->frames_per_stage;
     a.stages_per_seg = (plan->n_frames + plan->frames_per_stage - 1) / plan->frames_per_stage;
-    a.n_taps = (int)plan->wpad.size();
+    a.n_taps = (int)plan->mb.wpad.size();
     a.wpad = plan->d_wpad;
     a.mstart = plan->d_mstart;
-    a.n_groups = plan->n_groups;
-    a.pbuf_len = plan->pbuf_len;
-    for (int g = 0; g < 16; ++g) { a.gmax[g] = plan->gmax[g]; a.goff[g] = plan->goff[g]; }
+    a.n_groups = plan->mb.n_groups;
+    a.pbuf_len = plan->mb.pbuf_len;
+    for (int g = 0; g < 16; ++g) { a.gmax[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
     CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));

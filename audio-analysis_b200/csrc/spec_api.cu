@@ -1,0 +1,195 @@
+// C-ABI of the framed-spectrum paths (include/cacophony_b200.h, cac_spec_* and helpers):
+// identify_morepork._load_sample + window loop, identify_tracks.get_end, signal_noise's STFT.
+#include <cstring>
+#include <vector>
+
+#include "api_util.h"
+#include "cac_common.cuh"
+#include "mel_bands.h"
+#include "spec.cuh"
+
+using namespace cac;
+
+struct cac_spec_plan {
+    cac_spec_params p;
+    int device;
+    int kmin, nbins;
+    MelBands mb;
+    float2* d_ltab = nullptr;
+    float2* d_rtab = nullptr;
+    float* d_wpad = nullptr;
+    int* d_mstart = nullptr;
+    long long* d_tab = nullptr;   size_t tab_cap = 0;    // item tables staged per call
+    long long* d_wtab = nullptr;  size_t wtab_cap = 0;   // morepork window tables
+};
+
+extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* h_mel_weights, int device,
+                                    cac_spec_plan** out) {
+    if (!params || !out) return fail(CAC_ERR_INVALID, "null argument");
+    const cac_spec_params& p = *params;
+    if (p.n_fft != 4800 && p.n_fft != 1600 && p.n_fft != 4096)
+        return fail(CAC_ERR_INVALID,
+                    "framed-spectrum kernels are built for n_fft 4800 / 1600 (sr // 10 at 48 / 16 kHz) and 4096");
+    if (p.hop_length < 1 || p.hop_length > p.n_fft) return fail(CAC_ERR_INVALID, "hop_length out of range");
+    if (p.power != 1 && p.power != 2) return fail(CAC_ERR_INVALID, "power must be 1 or 2");
+    if (p.n_mels < 0 || p.n_mels > kMaxMels) return fail(CAC_ERR_INVALID, "n_mels out of range");
+    if (p.n_mels > 0 && !h_mel_weights) return fail(CAC_ERR_INVALID, "mel weights missing");
+    const int bins = 1 + p.n_fft / 2;
+    if (p.n_mels == 0 && (p.bin_lo < 0 || p.bin_hi > bins || p.bin_lo >= p.bin_hi))
+        return fail(CAC_ERR_INVALID, "bin range out of bounds");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+        return fail(CAC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU path)");
+    if (device < 0 || device >= ndev) return fail(CAC_ERR_INVALID, "device index out of range");
+    if (p.n_fft == 4096) return fail(CAC_ERR_INVALID, "the n_fft 4096 full-spectrum variant is not built yet");
+    CUDA_TRY(cudaSetDevice(device));
+
+    cac_spec_plan* plan = new cac_spec_plan();
+    plan->p = p;
+    plan->device = device;
+    if (p.n_mels > 0) {
+        const std::string berr = plan->mb.build(h_mel_weights, p.n_mels, bins);
+        if (!berr.empty()) { delete plan; return fail(CAC_ERR_INVALID, berr); }
+        if (plan->mb.n_groups > 16) { delete plan; return fail(CAC_ERR_INVALID, "n_mels > 512 is not supported"); }
+        plan->kmin = plan->mb.kmin;
+        plan->nbins = plan->mb.kmax - plan->mb.kmin + 1;
+    } else {
+        plan->kmin = p.bin_lo;
+        plan->nbins = p.bin_hi - p.bin_lo;
+    }
+    SpecArgs probe{};
+    probe.n_fft = p.n_fft;
+    probe.n_mels = p.n_mels;
+    probe.n_taps = (int)plan->mb.wpad.size();
+    probe.pbuf_len = plan->mb.pbuf_len;
+    if (spec4800_smem_bytes(probe) > 227 * 1024) {
+        delete plan;
+        return fail(CAC_ERR_INVALID, "filterbank exceeds the shared-memory budget of the 4800-point kernel");
+    }
+    std::vector<float2> lt(kSpec4800LtabRows * 32), rt(kSpec4800Rounds);
+    spec4800_host_tables(p.n_fft, plan->kmin, lt.data(), rt.data());
+    cudaError_t e = cudaMalloc((void**)&plan->d_ltab, lt.size() * sizeof(float2));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_rtab, rt.size() * sizeof(float2));
+    if (e == cudaSuccess) e = cudaMemcpy(plan->d_ltab, lt.data(), lt.size() * sizeof(float2), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(plan->d_rtab, rt.data(), rt.size() * sizeof(float2), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && p.n_mels > 0) {
+        e = cudaMalloc((void**)&plan->d_wpad, plan->mb.wpad.size() * sizeof(float) + 16);
+        if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_mstart, plan->mb.mstart.size() * sizeof(int) + 16);
+        if (e == cudaSuccess)
+            e = cudaMemcpy(plan->d_wpad, plan->mb.wpad.data(), plan->mb.wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess)
+            e = cudaMemcpy(plan->d_mstart, plan->mb.mstart.data(), plan->mb.mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) {
+        cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
+        delete plan;
+        return fail(CAC_ERR_ALLOC, std::string("could not upload the spectrum tables: ") + cudaGetErrorString(e));
+    }
+    *out = plan;
+    return CAC_OK;
+}
+
+extern "C" int cac_spec_plan_destroy(cac_spec_plan* plan) {
+    if (!plan) return CAC_OK;
+    cudaSetDevice(plan->device);
+    cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
+    cudaFree(plan->d_tab); cudaFree(plan->d_wtab);
+    delete plan;
+    return CAC_OK;
+}
+
+extern "C" int64_t cac_spec_frame_count(const cac_spec_plan* plan, int64_t n_samples) {
+    if (!plan || n_samples < 0) return CAC_ERR_INVALID;
+    return 1 + n_samples / plan->p.hop_length;
+}
+
+extern "C" int32_t cac_spec_rows(const cac_spec_plan* plan) {
+    if (!plan) return CAC_ERR_INVALID;
+    return plan->p.n_mels > 0 ? plan->p.n_mels : plan->nbins;
+}
+
+extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64_t* h_item_offset,
+                            const int64_t* h_item_samples, int64_t n_items, float* d_out, float* d_max, void* stream) {
+    if (!plan || !d_pcm || !h_item_offset || !h_item_samples || !d_out) return fail(CAC_ERR_INVALID, "null argument");
+    if (n_items < 0 || n_items > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_items out of range");
+    if (n_items == 0) return CAC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    std::vector<long long> tab(3 * (size_t)n_items + 1);          // [item_off | item_len | frame_base]
+    long long total = 0;
+    for (int64_t i = 0; i < n_items; ++i) {
+        if (h_item_offset[i] < 0 || h_item_samples[i] < 0) return fail(CAC_ERR_INVALID, "negative item offset/length");
+        tab[i] = h_item_offset[i];
+        tab[n_items + i] = h_item_samples[i];
+        tab[2 * n_items + i] = total;
+        total += 1 + h_item_samples[i] / plan->p.hop_length;
+    }
+    tab[3 * n_items] = total;
+    int rc = ensure_cap(&plan->d_tab, &plan->tab_cap, tab.size() * sizeof(long long));
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(plan->d_tab, tab.data(), tab.size() * sizeof(long long), cudaMemcpyHostToDevice, st));
+    if (d_max) CUDA_TRY(cudaMemsetAsync(d_max, 0, sizeof(float), st));
+    SpecArgs a{};
+    a.pcm = d_pcm;
+    a.item_off = plan->d_tab;
+    a.item_len = plan->d_tab + n_items;
+    a.frame_base = plan->d_tab + 2 * n_items;
+    a.n_items = (int)n_items;
+    a.n_frames_total = total;
+    a.n_fft = plan->p.n_fft;
+    a.hop = plan->p.hop_length;
+    a.power = plan->p.power;
+    a.kmin = plan->kmin;
+    a.nbins = plan->nbins;
+    a.n_mels = plan->p.n_mels;
+    a.bin_major = plan->p.bin_major;
+    a.out = d_out;
+    a.gmax = d_max;
+    a.ltab = plan->d_ltab;
+    a.rtab = plan->d_rtab;
+    a.wpad = plan->d_wpad;
+    a.mstart = plan->d_mstart;
+    a.n_taps = (int)plan->mb.wpad.size();
+    a.n_groups = plan->mb.n_groups;
+    a.pbuf_len = plan->mb.pbuf_len;
+    for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
+    CUDA_TRY(launch_spec4800(a, st));
+    return CAC_OK;
+}
+
+extern "C" int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int32_t chunk, float* d_out,
+                                    void* stream) {
+    if (!d_in || !d_out || n_rows < 1 || n_cols < 0 || chunk < 1) return fail(CAC_ERR_INVALID, "bad argument");
+    const long long n_chunks = n_cols / chunk;
+    if (n_chunks == 0) return CAC_OK;
+    CUDA_TRY(launch_chunk_minmax(d_in, n_rows, n_cols, chunk, n_chunks, reinterpret_cast<float2*>(d_out),
+                                 (cudaStream_t)stream));
+    return CAC_OK;
+}
+
+extern "C" int cac_scale_by_max_run(float* d_data, int64_t n, const float* d_max, void* stream) {
+    if (!d_data || !d_max || n < 0) return fail(CAC_ERR_INVALID, "bad argument");
+    if (n == 0) return CAC_OK;
+    CUDA_TRY(launch_scale_by_max(d_data, n, d_max, (cudaStream_t)stream));
+    return CAC_OK;
+}
+
+extern "C" int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec, const int64_t* h_win_frame0,
+                                        const int32_t* h_win_width, int64_t n_windows, float* d_out, void* stream) {
+    if (!plan || !d_spec || !h_win_frame0 || !h_win_width || !d_out) return fail(CAC_ERR_INVALID, "null argument");
+    if (plan->p.n_mels != 0 || plan->p.bin_major) return fail(CAC_ERR_INVALID, "needs a frame-major raw-band plan");
+    if (n_windows < 0) return fail(CAC_ERR_INVALID, "n_windows out of range");
+    if (n_windows == 0) return CAC_OK;
+    for (int64_t i = 0; i < n_windows; ++i)
+        if (h_win_width[i] < 0 || h_win_width[i] > 60 || h_win_frame0[i] < 0)
+            return fail(CAC_ERR_INVALID, "window out of range (width must be 0..60)");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    int rc = ensure_cap(&plan->d_wtab, &plan->wtab_cap, (size_t)n_windows * (sizeof(long long) + sizeof(int)));
+    if (rc) return rc;
+    int* d_width = reinterpret_cast<int*>(plan->d_wtab + n_windows);
+    CUDA_TRY(cudaMemcpyAsync(plan->d_wtab, h_win_frame0, (size_t)n_windows * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_width, h_win_width, (size_t)n_windows * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(launch_morepork_windows(d_spec, plan->d_wtab, d_width, n_windows, plan->nbins, d_out, st));
+    return CAC_OK;
+}

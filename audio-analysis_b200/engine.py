@@ -59,7 +59,25 @@ lib.cac_ci_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 lib.cac_ci_host.argtypes = [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _vp]
 lib.cac_ci_entries_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
-EXPORTS = ["cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
+
+
+class CacSpecParams(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("n_fft", "hop_length", "bin_lo", "bin_hi", "n_mels", "power",
+                                              "bin_major")]
+
+
+lib.cac_spec_plan_create.argtypes = [ctypes.POINTER(CacSpecParams), _vp, ctypes.c_int, ctypes.POINTER(_vp)]
+lib.cac_spec_plan_destroy.argtypes = [_vp]
+lib.cac_spec_frame_count.argtypes = [_vp, _i64]
+lib.cac_spec_frame_count.restype = _i64
+lib.cac_spec_rows.argtypes = [_vp]
+lib.cac_spec_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
+lib.cac_scale_by_max_run.argtypes = [_vp, _i64, _vp, _vp]
+lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
+lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
+
+EXPORTS = ["cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+           "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
@@ -281,3 +299,87 @@ class CiPlan:
                 check(lib.cac_ci_entries_run(self._h, points.data_ptr(), es.ctypes.data_as(_vp), el.ctypes.data_as(_vp),
                                              len(es), out.data_ptr(), _stream_ptr(torch)))
         return out.cpu().numpy()
+
+
+class SpecPlan:
+    """Framed-spectrum plan (cac_spec_*): librosa.stft framing -> |X|**power of selected bins,
+    optionally through a custommel filterbank."""
+
+    def __init__(self, n_fft, hop_length, bin_lo=0, bin_hi=0, n_mels=0, power=1, bin_major=False, mel_weights=None,
+                 device=0):
+        self.params = CacSpecParams(int(n_fft), int(hop_length), int(bin_lo), int(bin_hi), int(n_mels), int(power),
+                                    int(bool(bin_major)))
+        w = None
+        if n_mels:
+            w = np.ascontiguousarray(mel_weights, dtype=np.float32)
+            assert w.shape == (n_mels, 1 + n_fft // 2), w.shape
+        self.device = device
+        self.hop_length = int(hop_length)
+        self._h = ctypes.c_void_p()
+        check(lib.cac_spec_plan_create(ctypes.byref(self.params), w.ctypes.data_as(_vp) if w is not None else None,
+                                       device, ctypes.byref(self._h)))
+        self.rows = int(lib.cac_spec_rows(self._h))
+
+    def close(self):
+        if self._h:
+            lib.cac_spec_plan_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def frame_count(self, n_samples):
+        return 1 + int(n_samples) // self.hop_length
+
+    def run(self, pcm, item_offset, item_samples, out=None, want_max=False):
+        """pcm: flat CUDA float32 tensor.  Returns (out, frame_base[, max tensor]); `out` is a flat
+        CUDA float32 tensor of rows * total_frames values laid out as the plan's layout says."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        off = np.ascontiguousarray(item_offset, dtype=np.int64)
+        ns = np.ascontiguousarray(item_samples, dtype=np.int64)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        assert off.shape == ns.shape and (off + ns <= pcm.numel()).all()
+        base = np.concatenate([[0], np.cumsum(1 + ns // self.hop_length)]).astype(np.int64)
+        total = int(base[-1])
+        if out is None:
+            out = torch.empty((total * self.rows,), dtype=torch.float32, device=dev)
+        assert out.numel() >= total * self.rows
+        mx = torch.zeros((1,), dtype=torch.float32, device=dev) if want_max else None
+        with torch.cuda.device(dev):
+            check(lib.cac_spec_run(self._h, pcm.data_ptr(), off.ctypes.data_as(_vp), ns.ctypes.data_as(_vp), len(off),
+                                   out.data_ptr(), mx.data_ptr() if want_max else None, _stream_ptr(torch)))
+        return (out, base, mx) if want_max else (out, base)
+
+    def morepork_windows(self, spec, win_frame0, win_width, out=None):
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        f0 = np.ascontiguousarray(win_frame0, dtype=np.int64)
+        wd = np.ascontiguousarray(win_width, dtype=np.int32)
+        if out is None:
+            out = torch.empty((len(f0), self.rows, 60), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_morepork_windows_run(self._h, spec.data_ptr(), f0.ctypes.data_as(_vp), wd.ctypes.data_as(_vp),
+                                               len(f0), out.data_ptr(), _stream_ptr(torch)))
+        return out
+
+
+def chunk_minmax(x, chunk):
+    """(min, max) of x[:, c*chunk:(c+1)*chunk] for every complete chunk of a CUDA float32 [rows, cols] tensor."""
+    torch = _torch()
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+    n = x.shape[1] // chunk
+    out = torch.empty((n, 2), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.cac_chunk_minmax_run(x.data_ptr(), x.shape[0], x.shape[1], chunk, out.data_ptr(), _stream_ptr(torch)))
+    return out
+
+
+def scale_by_max(x, mx):
+    torch = _torch()
+    with torch.cuda.device(x.device):
+        check(lib.cac_scale_by_max_run(x.data_ptr(), x.numel(), mx.data_ptr(), _stream_ptr(torch)))
+    return x

@@ -135,3 +135,36 @@ def get_spect(data, sr, hop_length, mean_sub, use_mfcc, mel_break, htk, n_mels, 
                  11000 if fmin is None else fmax, mel_break, len(data), int(power), bool(db_scale), False)
     seg = np.array([(0, len(data), 0)], dtype=SEGMENT_DTYPE)
     return _finish(plan.run_host(data, seg), mean_sub, channels)[0]
+
+
+@functools.lru_cache(maxsize=4)
+def _get_end_plan(sr, device=0):
+    from . import engine
+    n_fft = sr // 10
+    w = custommel._mel_f_cached(sr, 120, 50, 11000, n_fft, 1750)
+    return engine.SpecPlan(n_fft, 281, n_mels=120, power=1, mel_weights=w, device=device)
+
+
+def get_end(frames, sr):
+    """src/identify_tracks.py:387-413: first 1-second chunk of the 120-mel magnitude spectrogram
+    (n_fft = sr // 10, hop 281) whose values are all equal (digital silence) -> its start in whole
+    seconds; else the file length.  STFT, mel and the per-chunk min/max run on the GPU."""
+    import torch
+    from . import engine
+    hop_length = 281
+    frames = np.ascontiguousarray(frames, dtype=np.float32)
+    plan = _get_end_plan(int(sr))
+    mel, base = plan.run(torch.from_numpy(frames).cuda(plan.device), [0], [frames.shape[0]])
+    n_frames = int(base[-1])
+    chunk_length = sr // hop_length
+    mm = engine.chunk_minmax(mel.view(120, n_frames), chunk_length).cpu().numpy()
+    start = 0
+    end = start + chunk_length
+    file_length = len(frames) / sr
+    while end < n_frames:
+        lo, hi = mm[start // chunk_length]
+        if hi == lo:
+            return start * hop_length // sr
+        start = end
+        end = start + chunk_length
+    return file_length

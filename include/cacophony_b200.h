@@ -135,6 +135,46 @@ int cac_ci_host(cac_ci_plan* plan, const float* h_pcm, int64_t n_pcm, const int6
 int cac_ci_entries_run(cac_ci_plan* plan, const uint8_t* d_points, const int64_t* h_entry_start,
                        const int32_t* h_entry_len, int64_t n_entries, int32_t* d_out, void* stream);
 
+/* ---- framed spectra: identify_morepork, get_end, signal_noise's STFT --------------------------------
+ * librosa.stft(frames, n_fft, hop_length) with its defaults (periodic Hann, centre = True, zero
+ * padding, 1 + len // hop frames) followed by |.|**power, restricted to the FFT bins the caller
+ * consumes, optionally projected through a custommel.mel_f filterbank. */
+typedef struct cac_spec_params {
+    int32_t n_fft;        /* 4800 = int(sr / 10) at 48 kHz (src/identify_morepork.py:23, src/identify_tracks.py:389) */
+    int32_t hop_length;   /* int(n_fft / 2) for morepork (:24); 281 for get_end (:388) */
+    int32_t bin_lo;       /* raw output (n_mels == 0): FFT bins [bin_lo, bin_hi); morepork 60:120 (:25) */
+    int32_t bin_hi;
+    int32_t n_mels;       /* > 0: mel projection (src/custommel.py:59-63); get_end uses 120 (:390-399) */
+    int32_t power;        /* 1 or 2 */
+    int32_t bin_major;    /* raw output layout: 0 = [frame][bin] over all frames, 1 = per recording [bin][frame] */
+} cac_spec_params;
+typedef struct cac_spec_plan cac_spec_plan;
+
+int cac_spec_plan_create(const cac_spec_params* params, const float* h_mel_weights, int device,
+                         cac_spec_plan** out);
+int cac_spec_plan_destroy(cac_spec_plan* plan);
+/* 1 + n_samples // hop_length */
+int64_t cac_spec_frame_count(const cac_spec_plan* plan, int64_t n_samples);
+/* rows per frame of the output: n_mels, or bin_hi - bin_lo */
+int32_t cac_spec_rows(const cac_spec_plan* plan);
+/* Spectra of n_items recordings stored in d_pcm at h_item_offset[i] (h_item_samples[i] samples).
+ * Frames are numbered globally, recording after recording.  Output: mel -> per recording
+ * [n_mels][frames_i] (recordings back to back); raw -> see bin_major.  d_max (may be NULL)
+ * receives the largest |X|**power produced (signal_noise's a_max, src/identify_tracks.py:656). */
+int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64_t* h_item_offset, const int64_t* h_item_samples,
+                 int64_t n_items, float* d_out, float* d_max, void* stream);
+/* d_data[i] /= *d_max  (spectogram / a_max, src/identify_tracks.py:657) */
+int cac_scale_by_max_run(float* d_data, int64_t n, const float* d_max, void* stream);
+/* get_end's chunk scan (src/identify_tracks.py:404-412): d_out[c] = {min, max} of
+ * d_in[:, c*chunk : (c+1)*chunk] for the n_cols // chunk complete chunks of a row-major [n_rows][n_cols] matrix. */
+int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int32_t chunk, float* d_out, void* stream);
+/* identify_morepork's window loop body (src/identify_morepork.py:150-166): window w covers
+ * h_win_width[w] (<= 60) frames of the frame-major raw spectrum d_spec starting at global frame
+ * h_win_frame0[w]; librosa.amplitude_to_db(ref=np.max), rescale by |min|, zero-pad to 60 columns;
+ * d_out[w][bin][60]. */
+int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec, const int64_t* h_win_frame0,
+                             const int32_t* h_win_width, int64_t n_windows, float* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
