@@ -41,7 +41,6 @@ extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* 
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
         return fail(CAC_ERR_NO_DEVICE, "no CUDA device (this library has no CPU path)");
     if (device < 0 || device >= ndev) return fail(CAC_ERR_INVALID, "device index out of range");
-    if (p.n_fft == 4096) return fail(CAC_ERR_INVALID, "the n_fft 4096 full-spectrum variant is not built yet");
     CUDA_TRY(cudaSetDevice(device));
 
     cac_spec_plan* plan = new cac_spec_plan();

@@ -355,6 +355,7 @@ cudaError_t launch_spec4800(const SpecArgs& a, cudaStream_t st) {
     void (*kern)(const SpecArgs) = nullptr;
     if (a.n_fft == 4800) kern = spec4800_kernel<75>;
     else if (a.n_fft == 1600) kern = spec4800_kernel<25>;
+    else if (a.n_fft == 4096) kern = spec4800_kernel<64>;   // signal_noise's full spectrum (src/identify_tracks.py:652-654)
     else return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -76,7 +76,9 @@ lib.cac_scale_by_max_run.argtypes = [_vp, _i64, _vp, _vp]
 lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
 lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
-EXPORTS = ["cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
+
+EXPORTS = ["cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
@@ -383,3 +385,15 @@ def scale_by_max(x, mx):
     with torch.cuda.device(x.device):
         check(lib.cac_scale_by_max_run(x.data_ptr(), x.numel(), mx.data_ptr(), _stream_ptr(torch)))
     return x
+
+
+def magtransform(x, a, device=0):
+    """x ** sigmoid(a) (MagTransform.call) on a numpy array or CUDA float32 tensor."""
+    torch = _torch()
+    dev = torch.device("cuda", device)
+    was_np = isinstance(x, np.ndarray)
+    t = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32) if was_np else x).to(dev).contiguous()
+    out = torch.empty_like(t)
+    with torch.cuda.device(dev):
+        check(lib.cac_magtransform_run(t.data_ptr(), out.data_ptr(), t.numel(), float(a), _stream_ptr(torch)))
+    return out.cpu().numpy() if was_np else out

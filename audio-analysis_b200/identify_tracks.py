@@ -168,3 +168,22 @@ def get_end(frames, sr):
         start = end
         end = start + chunk_length
     return file_length
+
+
+@functools.lru_cache(maxsize=4)
+def _signal_noise_plan(hop_length, device=0):
+    from . import engine
+    return engine.SpecPlan(4096, hop_length, bin_lo=0, bin_hi=2049, n_mels=0, power=1, bin_major=True, device=device)
+
+
+def signal_noise_spectrogram(frames, sr, hop_length=281):
+    """First stage of signal_noise (src/identify_tracks.py:650-657): |STFT(n_fft=4096, hop)| of the
+    whole recording divided by its maximum, as a CUDA float32 tensor [2049, n_frames] that stays on
+    the device for the median / morphology stages."""
+    import torch
+    from . import engine
+    frames = np.ascontiguousarray(frames, dtype=np.float32)
+    plan = _signal_noise_plan(int(hop_length))
+    spec, base, a_max = plan.run(torch.from_numpy(frames).cuda(plan.device), [0], [frames.shape[0]], want_max=True)
+    engine.scale_by_max(spec, a_max)
+    return spec.view(2049, int(base[-1]))

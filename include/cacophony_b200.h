@@ -175,6 +175,10 @@ int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int3
 int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec, const int64_t* h_win_frame0,
                              const int32_t* h_win_width, int64_t n_windows, float* d_out, void* stream);
 
+/* MagTransform.call (src/magtransform.py:17-19, src/magtransformv2.py:19-21): d_out = d_in ** sigmoid(a),
+ * elementwise float32 (in place allowed); `a` is the layer's learned scalar (v1 init 0.0, v2 init -1.0). */
+int cac_magtransform_run(const float* d_in, float* d_out, int64_t n, float a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

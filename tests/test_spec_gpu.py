@@ -117,3 +117,28 @@ def test_spec_plan_rejects_unsupported(engine):
         engine.SpecPlan(4410, 2205, bin_lo=60, bin_hi=120)
     with pytest.raises(engine.CacError):
         engine.SpecPlan(4800, 2400, bin_lo=100, bin_hi=3000)
+
+
+def test_signal_noise_spectrogram_vs_reference_fixture(engine, golden):
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("get_end")
+    rec = synth.recording(1234, seconds=12.0)
+    got = T.signal_noise_spectrogram(rec[:96000], 48000).cpu().numpy()
+    assert got.shape == tuple(g["signal_noise_shape"]) == (2049, 1 + 96000 // 281)
+    ref_sub = g["signal_noise_sub"]                     # the reference's own output, every 8th row / column
+    assert np.abs(got[::8, ::8] - ref_sub).max() <= 2e-6
+    ref = O.signal_noise_spectrogram(rec[:96000], 48000)
+    assert got.max() == 1.0
+    _check_mag(got, ref)
+
+
+def test_magtransform_vs_reference_fixture(engine, golden):
+    from audio_analysis_b200 import magtransform as M1, magtransformv2 as M2
+    g = golden("magtransform")
+    x = g["x"]
+    y1, y2 = M1.MagTransform()(x), M2.MagTransform()(x)
+    assert y1.dtype == np.float32 and y1.shape == x.shape
+    assert np.allclose(y1, g["v1"], rtol=2e-6, atol=0) and np.allclose(y2, g["v2"], rtol=2e-6, atol=0)
+    big = np.abs(np.random.default_rng(0).standard_normal(100003)).astype(np.float32) * 50
+    assert np.allclose(M1.MagTransform(a=0.7)(big), O.magtransform(big, 0.7), rtol=2e-6, atol=0)
+    assert float(M2.MagTransform().a) == -1.0 and float(M1.MagTransform().a) == 0.0

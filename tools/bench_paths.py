@@ -57,14 +57,14 @@ def bench_morepork(n_rec=4096):
     n_rec = int(os.environ.get("CAC_MOREPORK_RECORDINGS", n_rec))
     reps = (n_rec + len(pool) - 1) // len(pool)
     pcm = torch.from_numpy(pool).cuda().repeat(reps, 1)[:n_rec].contiguous()
-    plan = M._plan(48000)
+    plan = M.BatchPlan(48000, pcm.shape[1])
     out = None
 
     def step():
         nonlocal out
-        out = plan.run(pcm, out=out)
+        out = plan.run(pcm, out=out)[0]
     ms = timed(step, steps=5)
-    algo = pcm.numel() * 4 + out[0].numel() * 4
+    algo = pcm.numel() * 4 + out.numel() * 4
     print(json.dumps({"path": "identify_morepork (configs[2])", "recordings": n_rec, "ms": ms,
                       "recording_hours_per_s": n_rec / 60.0 / (ms * 1e-3), "algorithmic_GBps": algo / ms / 1e6,
                       "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "dtype": "f32"}), flush=True)
