@@ -1,6 +1,7 @@
 // C-ABI of libcacophony_b200.so (see include/cacophony_b200.h for the contract and the
 // reference callables each entry point replaces).  No CPU fallback: without a CUDA device
 // every compute entry point fails with CAC_ERR_NO_DEVICE / CAC_ERR_CUDA.
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -50,6 +51,9 @@ struct cac_plan {
     void* d_work = nullptr;      size_t work_cap = 0;
     // optional CUDA events bracketing the dominant (stft_mel) kernel of the last cac_features_run
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // cac_features_host pipeline: upload / compute / download streams and per-chunk events
+    cudaStream_t s_h2d = nullptr, s_comp = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_up, ev_done;
 };
 
 extern "C" const char* cac_version(void) { return "cacophony_b200 0.1.0 (sm_100a)"; }
@@ -135,6 +139,9 @@ extern "C" int cac_plan_destroy(cac_plan* plan) {
     if (!plan) return CAC_OK;
     cudaSetDevice(plan->device);
     if (plan->ev0) { cudaEventDestroy(plan->ev0); cudaEventDestroy(plan->ev1); }
+    for (cudaEvent_t e : plan->ev_up) cudaEventDestroy(e);
+    for (cudaEvent_t e : plan->ev_done) cudaEventDestroy(e);
+    if (plan->s_h2d) { cudaStreamDestroy(plan->s_h2d); cudaStreamDestroy(plan->s_comp); cudaStreamDestroy(plan->s_d2h); }
     cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
     cudaFree(plan->d_pcm); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
@@ -217,17 +224,73 @@ extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_p
             s.pcm_offset < 0 || s.pcm_offset + s.n_valid > n_pcm)
             return fail(CAC_ERR_INVALID, "segment descriptor out of bounds");
     }
-    const size_t out_bytes = (size_t)n * plan->p.n_mels * plan->n_frames * sizeof(float);
+    const size_t item = (size_t)plan->p.n_mels * plan->n_frames;
+    const size_t out_bytes = (size_t)n * item * sizeof(float);
     int rc;
     if ((rc = ensure_cap(&plan->d_pcm, &plan->pcm_cap, (size_t)n_pcm * sizeof(float) + 16))) return rc;
     if ((rc = ensure_cap(&plan->d_segs, &plan->segs_cap, (size_t)n * sizeof(cac_segment)))) return rc;
     if ((rc = ensure_cap(&plan->d_out, &plan->out_cap, out_bytes))) return rc;
-    if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, cac_features_work_bytes(plan, n)))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(plan->d_pcm, h_pcm, (size_t)n_pcm * sizeof(float), cudaMemcpyHostToDevice, 0));
-    CUDA_TRY(cudaMemcpyAsync(plan->d_segs, h_segs, (size_t)n * sizeof(cac_segment), cudaMemcpyHostToDevice, 0));
-    if ((rc = cac_features_run(plan, plan->d_pcm, plan->d_segs, n, plan->d_out, plan->d_work, nullptr))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(h_out, plan->d_out, out_bytes, cudaMemcpyDeviceToHost, 0));
-    CUDA_TRY(cudaStreamSynchronize(0));
+    // Pipeline: the PCM goes up in pieces on one stream, segment chunks are transformed on a second
+    // stream as soon as the samples they reference have arrived, and every finished chunk goes back to
+    // the host on a third stream - upload, kernels and download overlap (full-duplex PCIe) when the
+    // host buffers are page-locked; with pageable buffers the copies serialise but stay correct.
+    const int n_chunks = (int)std::min<int64_t>(16, (n + 73) / 74);
+    const int64_t per_chunk = (n + n_chunks - 1) / n_chunks;
+    const size_t work_chunk = (cac_features_work_bytes(plan, per_chunk) + 255) / 256 * 256;
+    if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, work_chunk * n_chunks))) return rc;
+    if (!plan->s_h2d) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&plan->s_h2d, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&plan->s_comp, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&plan->s_d2h, cudaStreamNonBlocking));
+    }
+    while ((int)plan->ev_up.size() < n_chunks) {
+        cudaEvent_t a, b;
+        CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        plan->ev_up.push_back(a);
+        plan->ev_done.push_back(b);
+    }
+    CUDA_TRY(cudaMemcpyAsync(plan->d_segs, h_segs, (size_t)n * sizeof(cac_segment), cudaMemcpyHostToDevice, plan->s_h2d));
+    // upload piece c = samples up to the furthest one any segment of chunks 0..c touches
+    int64_t sent = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+        const int64_t s0 = c * per_chunk, s1 = std::min<int64_t>(n, s0 + per_chunk);
+        int64_t need = sent;
+        for (int64_t i = s0; i < s1; ++i) need = std::max<int64_t>(need, h_segs[i].pcm_offset + h_segs[i].n_valid);
+        need = std::min<int64_t>(n_pcm, (need + 3) / 4 * 4);
+        if (need > sent) {
+            CUDA_TRY(cudaMemcpyAsync(plan->d_pcm + sent, h_pcm + sent, (size_t)(need - sent) * sizeof(float),
+                                     cudaMemcpyHostToDevice, plan->s_h2d));
+            sent = need;
+        }
+        CUDA_TRY(cudaEventRecord(plan->ev_up[c], plan->s_h2d));
+    }
+    for (int c = 0; c < n_chunks; ++c) {
+        const int64_t s0 = c * per_chunk, s1 = std::min<int64_t>(n, s0 + per_chunk);
+        if (s1 <= s0) break;
+        CUDA_TRY(cudaStreamWaitEvent(plan->s_comp, plan->ev_up[c], 0));
+        if ((rc = cac_features_run(plan, plan->d_pcm, plan->d_segs + s0, s1 - s0, plan->d_out + s0 * item,
+                                   (char*)plan->d_work + work_chunk * c, plan->s_comp)))
+            return rc;
+        CUDA_TRY(cudaEventRecord(plan->ev_done[c], plan->s_comp));
+        CUDA_TRY(cudaStreamWaitEvent(plan->s_d2h, plan->ev_done[c], 0));
+        CUDA_TRY(cudaMemcpyAsync(h_out + s0 * item, plan->d_out + s0 * item, (size_t)(s1 - s0) * item * sizeof(float),
+                                 cudaMemcpyDeviceToHost, plan->s_d2h));
+    }
+    CUDA_TRY(cudaStreamSynchronize(plan->s_d2h));
+    CUDA_TRY(cudaStreamSynchronize(plan->s_comp));
+    return CAC_OK;
+}
+
+extern "C" int cac_host_register(void* h_ptr, size_t bytes) {
+    if (!h_ptr || bytes == 0) return fail(CAC_ERR_INVALID, "bad argument");
+    CUDA_TRY(cudaHostRegister(h_ptr, bytes, cudaHostRegisterDefault));
+    return CAC_OK;
+}
+
+extern "C" int cac_host_unregister(void* h_ptr) {
+    if (!h_ptr) return fail(CAC_ERR_INVALID, "bad argument");
+    CUDA_TRY(cudaHostUnregister(h_ptr));
     return CAC_OK;
 }
 

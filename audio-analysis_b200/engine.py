@@ -76,9 +76,11 @@ lib.cac_scale_by_max_run.argtypes = [_vp, _i64, _vp, _vp]
 lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
 lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
+lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
+lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
 
-EXPORTS = ["cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
@@ -166,6 +168,13 @@ class FeaturePlan:
             check(lib.cac_features_run(self._h, pcm.data_ptr(), segments.data_ptr(), n, out.data_ptr(),
                                        self._work.data_ptr(), _stream_ptr(torch)))
         return out
+
+    def last_segment_max(self, n):
+        """Per-segment maximum mel power of the last run() over n segments (the power_to_db reference
+        value, kept in the work buffer): CUDA float32 view [n] - a small per-segment result to gather."""
+        torch = _torch()
+        off = ((n * 8 + 127) // 128) * 128
+        return self._work[off:off + 4 * n].view(torch.float32)
 
     # ---- host-buffer path (H2D + run + D2H inside the call) ----------------------------------
     def run_host(self, pcm, segments, out=None):
@@ -397,3 +406,18 @@ def magtransform(x, a, device=0):
     with torch.cuda.device(dev):
         check(lib.cac_magtransform_run(t.data_ptr(), out.data_ptr(), t.numel(), float(a), _stream_ptr(torch)))
     return out.cpu().numpy() if was_np else out
+
+
+class pinned:
+    """Context manager page-locking a numpy array for the duration of *_host calls (cac_host_register)."""
+
+    def __init__(self, arr):
+        self.arr = arr
+
+    def __enter__(self):
+        check(lib.cac_host_register(self.arr.ctypes.data_as(_vp), self.arr.nbytes))
+        return self.arr
+
+    def __exit__(self, *exc):
+        lib.cac_host_unregister(self.arr.ctypes.data_as(_vp))
+        return False

@@ -169,7 +169,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from audio_analysis_b200 import engine, identify_tracks as T
+    from audio_analysis_b200 import engine, identify_tracks as T, sharding
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -205,16 +205,24 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def step():
+        """one pass of the hot path over this rank's recordings + (N > 1) the per-recording result gather"""
+        plan.run(pcm, segs_dev, out)
+        if world > 1:
+            per_rec = plan.last_segment_max(N_REC * nseg1).view(N_REC, nseg1)
+            return sharding.gather_per_recording(per_rec, world * N_REC)
+        return None
+
     # ---- device-resident timing ---------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
-        plan.run(pcm, segs_dev, out)
+        step()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
     ev0.record()
     for _ in range(args.steps):
-        plan.run(pcm, segs_dev, out)
+        gathered = step()
     ev1.record()
     barrier()
     total_ms = ev0.elapsed_time(ev1)
@@ -224,6 +232,8 @@ def main():
         kernel_ms.append(plan.last_kernel_ms())
     clocks = sampler.stop() if sampler else None
     checksum = float(out[:nseg1].double().sum().item())
+    if gathered is not None:
+        assert gathered.shape == (world * N_REC, nseg1) and bool((gathered > 0).all())
 
     # ---- end to end through host buffers (pinned H2D of the inputs + D2H of the result per step) -----
     chunk = POOL
@@ -281,7 +291,7 @@ def main():
         "e2e": {"value": rec_hours / e2e_s, "unit": "recording-hours/s",
                 "h2d_bytes_per_step": int(n_chunks * (pool_np.nbytes + seg_chunk.nbytes)),
                 "d2h_bytes_per_step": int(n_chunks * out_host.nbytes), "ms_per_step": e2e_s * 1e3,
-                "api": "FeaturePlan.run_host -> cac_features_host, %d recordings per call" % chunk},
+                "api": "FeaturePlan.run_host -> cac_features_host (3-stream upload/compute/download pipeline, pinned host buffers), %d recordings per call" % chunk},
         "gpu_launches": 3 * args.steps,
         "kernels_per_step": ["seg_minmax_kernel", "stft_mel_kernel<2>", "power_to_db_kernel"],
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",

@@ -83,9 +83,14 @@ size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
  * d_out[s][m][f] float32 [n_segments, n_mels, frames] = get_spect(normalize_data(segment s)). */
 int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_segment* d_segments,
                      int64_t n_segments, float* d_out, void* d_work, void* stream);
-/* Same through host buffers (H2D of pcm + descriptors, run, D2H of the result, synchronise). */
+/* Same through host buffers: the PCM upload, the kernels and the download of finished segment chunks
+ * run on three streams and overlap when h_pcm / h_out are page-locked (cac_host_register, or any
+ * cudaHostAlloc'ed / torch pin_memory buffer); returns after the last byte of h_out has landed. */
 int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segments,
                       int64_t n_segments, float* h_out);
+/* Page-lock / release a caller-owned host buffer (cudaHostRegister) so that *_host calls can overlap copies. */
+int cac_host_register(void* h_ptr, size_t bytes);
+int cac_host_unregister(void* h_ptr);
 
 /* normalize_data (src/identify_tracks.py:202-209) on n_rows rows of row_len samples (bit-exact op order). */
 int cac_normalize_run(const float* d_in, float* d_out, int64_t n_rows, int32_t row_len, void* stream);
