@@ -33,7 +33,7 @@ S1 = dict(hop_length=281, mel_break=1750, n_mels=160, fmin=50, fmax=11000, power
 SEG_LEN, STRIDE = 3.0, 1.5
 ALGO_BYTES_PER_REC = 11_520_000 + 39 * 160 * 513 * 4          # unique PCM in + dB out
 FLOP_PER_REC = 2.65e9
-FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12              # nominal CUDA-core peak (not measured)
+FP32_PEAK_TFLOPS = 73.8     # measured on this pool: 36.9 T FFMA lane-ops/s (tools/micro/fp32x2_bench.cu, profiles/r1h_summary.md)
 
 
 def _gen(seed):
@@ -298,7 +298,7 @@ def main():
                      "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "stft_mel_kernel<2>",
                      "kernel_ms": k_ms, "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback",
                      "fp32_tflops": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12,
-                     "fp32_frac_of_nominal_peak": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12 / FP32_PEAK_TFLOPS,
+                     "fp32_frac_of_measured_peak": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12 / FP32_PEAK_TFLOPS,
                      "note": "FP32-pipe bound (75-110 flop/B, SURVEY.md 8d); HBM fraction reported as the metric asks"},
         "clocks": clocks, "checksum_first_recording": checksum,
     }
