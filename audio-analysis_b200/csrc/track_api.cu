@@ -1,0 +1,74 @@
+// C-ABI of signal_noise's post-STFT stage (include/cacophony_b200.h, cac_signal_components).
+#include <vector>
+
+#include "api_util.h"
+#include "cac_common.cuh"
+#include "track_signals.cuh"
+
+using namespace cac;
+
+namespace {
+struct Scratch {   // freed on every exit path
+    void* p[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    ~Scratch() { for (void* q : p) if (q) cudaFree(q); }
+};
+}  // namespace
+
+extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                                     int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
+                                     uint8_t* d_stage_masks, void* stream) {
+    if (!d_spec || !h_stats || !h_count) return fail(CAC_ERR_INVALID, "null argument");
+    if (rows < 1 || cols < 1 || (int64_t)rows * cols > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "matrix size out of range");
+    if (dilate_h < 1 || dilate_w < 1 || erode_h < 1 || dilate_h > 255 || dilate_w > 4096 || max_components < 1)
+        return fail(CAC_ERR_INVALID, "kernel size / max_components out of range");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t n = (size_t)rows * cols;
+    Scratch s;
+    float *d_t, *d_med;
+    unsigned char *m0, *m1, *m2;
+    int* d_small;
+    // d_t doubles as the label array later (same size: 4 bytes per cell)
+    CUDA_TRY(cudaMalloc(&s.p[0], n * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.p[1], n * sizeof(int)));
+    CUDA_TRY(cudaMalloc(&s.p[2], 3 * n));
+    CUDA_TRY(cudaMalloc(&s.p[3], ((size_t)rows + cols) * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int)));
+    d_t = (float*)s.p[0];
+    int* d_rootid = (int*)s.p[1];
+    m0 = (unsigned char*)s.p[2]; m1 = m0 + n; m2 = m1 + n;
+    d_med = (float*)s.p[3];
+    d_small = (int*)s.p[4];
+    float* rowmed = d_med;
+    float* colmed = d_med + rows;
+
+    // medians: rows directly, columns as rows of the transposed matrix (:658-659)
+    CUDA_TRY(launch_row_median(d_spec, rowmed, rows, cols, st));
+    CUDA_TRY(launch_transpose(d_spec, d_t, rows, cols, st));
+    CUDA_TRY(launch_row_median(d_t, colmed, cols, rows, st));
+    CUDA_TRY(launch_signal_mask(d_spec, rowmed, colmed, m0, rows, cols, st));
+    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks, m0, n, cudaMemcpyDeviceToDevice, st));
+    // cv2.morphologyEx(MORPH_OPEN, ones((4, 4))) = erode then dilate (:669-671)
+    CUDA_TRY(launch_morph_rect(m0, m1, m2, rows, cols, 4, 4, false, st));
+    CUDA_TRY(launch_morph_rect(m2, m1, m0, rows, cols, 4, 4, true, st));
+    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks + n, m0, n, cudaMemcpyDeviceToDevice, st));
+    // cv2.dilate(ones((height, width))) then cv2.erode(ones((height // 10, width))) (:683-684)
+    CUDA_TRY(launch_morph_rect(m0, m1, m2, rows, cols, dilate_h, dilate_w, true, st));
+    CUDA_TRY(launch_morph_rect(m2, m1, m0, rows, cols, erode_h, dilate_w, false, st));
+    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks + 2 * n, m0, n, cudaMemcpyDeviceToDevice, st));
+    // cv2.connectedComponentsWithStats (8-connectivity) (:686)
+    int* d_stats = d_small + 4;
+    CUDA_TRY(launch_ccl(m0, (int*)d_t, d_rootid, rows, (int)cols, d_small, d_stats, max_components, st));
+    int count = 0;
+    CUDA_TRY(cudaMemcpyAsync(&count, d_small, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (count > max_components) return fail(CAC_ERR_INVALID, "more connected components than max_components");
+    std::vector<int> raw((size_t)count * 6);
+    if (count) CUDA_TRY(cudaMemcpy(raw.data(), d_stats, raw.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < count; ++i) {       // cv2 stats layout: x, y, width, height, area (+ our label-order key)
+        const int* r = raw.data() + 6 * i;
+        int32_t* o = h_stats + 6 * i;
+        o[0] = r[0]; o[1] = r[1]; o[2] = r[2] - r[0] + 1; o[3] = r[3] - r[1] + 1; o[4] = r[4]; o[5] = r[5];
+    }
+    *h_count = count;
+    return CAC_OK;
+}

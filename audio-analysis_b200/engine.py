@@ -76,11 +76,12 @@ lib.cac_scale_by_max_run.argtypes = [_vp, _i64, _vp, _vp]
 lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
 lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
+lib.cac_signal_components.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]
 lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
 
-EXPORTS = ["cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
@@ -421,3 +422,20 @@ class pinned:
     def __exit__(self, *exc):
         lib.cac_host_unregister(self.arr.ctypes.data_as(_vp))
         return False
+
+
+def signal_components(spec, dilate_h, dilate_w, erode_h, max_components=65536, want_masks=False):
+    """cac_signal_components on a CUDA float32 [rows, cols] normalised spectrogram: returns the int32
+    numpy array [n, 6] = (x, y, width, height, area, order) (and the three stage masks if asked)."""
+    torch = _torch()
+    assert spec.is_cuda and spec.dtype == torch.float32 and spec.is_contiguous() and spec.dim() == 2
+    rows, cols = spec.shape
+    stats = np.empty((max_components, 6), dtype=np.int32)
+    count = ctypes.c_int32(0)
+    masks = torch.empty((3, rows, cols), dtype=torch.uint8, device=spec.device) if want_masks else None
+    with torch.cuda.device(spec.device):
+        check(lib.cac_signal_components(spec.data_ptr(), rows, cols, int(dilate_h), int(dilate_w), int(erode_h),
+                                        int(max_components), stats.ctypes.data_as(_vp), ctypes.byref(count),
+                                        masks.data_ptr() if want_masks else None, _stream_ptr(torch)))
+    stats = stats[:count.value].copy()
+    return (stats, masks) if want_masks else stats

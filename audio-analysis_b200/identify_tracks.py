@@ -187,3 +187,33 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
     spec, base, a_max = plan.run(torch.from_numpy(frames).cuda(plan.device), [0], [frames.shape[0]], want_max=True)
     engine.scale_by_max(spec, a_max)
     return spec.view(2049, int(base[-1]))
+
+
+SIGNAL_WIDTH = 0.25   # src/identify_tracks.py:21
+
+
+def signal_noise(frames, sr, hop_length=281):
+    """src/identify_tracks.py:650-706: candidate track signals of a recording.  STFT magnitude,
+    medians, threshold, morphology and connected components run on the GPU
+    (signal_noise_spectrogram + engine.signal_components); the handful of component boxes comes back
+    to the host, where the reference's filter (:689-691) and time / frequency conversion (:697-704,
+    including its hard-coded 281) are applied.  Returns a list of Signal."""
+    from . import engine
+    n_fft = 4096
+    spec = signal_noise_spectrogram(frames, sr, hop_length)
+    width = int(SIGNAL_WIDTH * sr / hop_length)
+    freqs = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)                  # librosa.fft_frequencies
+    above = np.nonzero(freqs > 100)[0]
+    height = int(above[0]) + 1 if len(above) else 0
+    stats = engine.signal_components(spec, height, width, height // 10)
+    stats = stats[np.argsort(stats[:, 5], kind="stable")]         # cv2's label order ...
+    stats = stats[np.argsort(stats[:, 0], kind="stable")]         # ... then sorted(stats, key=x) (stable)
+    min_width = 0.65 * width
+    min_height = height - height // 10
+    signals = []
+    for x, y, w, h, _, _ in stats.tolist():
+        if not (w > min_width and h > min_height):
+            continue
+        max_freq = min(len(freqs) - 1, y + h)
+        signals.append(Signal(x * 281 / sr, (x + w) * 281 / sr, freqs[y], freqs[max_freq]))
+    return signals

@@ -180,6 +180,19 @@ int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int3
 int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec, const int64_t* h_win_frame0,
                              const int32_t* h_win_width, int64_t n_windows, float* d_out, void* stream);
 
+/* signal_noise after its STFT (src/identify_tracks.py:658-691) on the normalised magnitude spectrogram
+ * d_spec [rows][cols] (rows = FFT bins, cols = frames; what cac_spec_run + cac_scale_by_max_run leave on
+ * the device): np.median along both axes, signal = (spec > 3 col_median) & (spec > 3 row_median),
+ * cv2.morphologyEx(MORPH_OPEN, ones((4,4))), cv2.dilate(ones((dilate_h, dilate_w))),
+ * cv2.erode(ones((erode_h, dilate_w))), cv2.connectedComponentsWithStats (8-connected).
+ * h_stats[i] = {x, y, width, height, area, order} for the *h_count components (background excluded);
+ * `order` sorts components like cv2's labels (first 2x2 block in raster order).  d_stage_masks (may
+ * be NULL) receives the three uint8 [rows][cols] masks (threshold, opened, closed).  Synchronous; allocates
+ * and frees its own scratch. */
+int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                          int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
+                          uint8_t* d_stage_masks, void* stream);
+
 /* MagTransform.call (src/magtransform.py:17-19, src/magtransformv2.py:19-21): d_out = d_in ** sigmoid(a),
  * elementwise float32 (in place allowed); `a` is the layer's learned scalar (v1 init 0.0, v2 init -1.0). */
 int cac_magtransform_run(const float* d_in, float* d_out, int64_t n, float a, void* stream);

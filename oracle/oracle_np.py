@@ -247,6 +247,50 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
     return spectogram / np.amax(spectogram)
 
 
+SIGNAL_WIDTH = 0.25
+
+
+def signal_noise_stages(frames, sr, hop_length=281):
+    """signal_noise (src/identify_tracks.py:650-706) with its intermediates: returns
+    (signals, mask, opened, closed, stats) where signals = [(start, end, freq_start, freq_end)],
+    mask = the 3x-median threshold (:667), opened = after the 4x4 MORPH_OPEN (:671),
+    closed = after dilate (height, width) / erode (height // 10, width) (:683-684), stats = the
+    filtered, x-sorted component stats (:686-691).  cv2 is the reference's own dependency."""
+    import cv2
+    n_fft = 4096
+    spectogram = np.abs(stft(frames, n_fft, hop_length))
+    a_max = np.amax(spectogram)
+    spectogram = spectogram / a_max
+    row_medians = np.median(spectogram, axis=1)
+    column_medians = np.median(spectogram, axis=0)
+    signal = (spectogram > 3 * column_medians[np.newaxis, :]) & (spectogram > 3 * row_medians[:, np.newaxis])
+    mask = signal.astype(np.uint8)
+    opened = cv2.morphologyEx(mask, cv2.MORPH_OPEN, np.ones((4, 4), np.uint8))
+    width = int(SIGNAL_WIDTH * sr / hop_length)
+    freqs = fft_frequencies(sr, n_fft)
+    height = 0
+    for i, f in enumerate(freqs):
+        if f > 100:
+            height = i + 1
+            break
+    closed = cv2.dilate(opened, np.ones((height, width), np.uint8))
+    closed = cv2.erode(closed, np.ones((height // 10, width), np.uint8))
+    _, _, stats, _ = cv2.connectedComponentsWithStats(closed)
+    stats = sorted(stats[1:], key=lambda stat: stat[0])
+    min_width = 0.65 * width
+    min_height = height - height // 10
+    stats = [st for st in stats if st[2] > min_width and st[3] > min_height]
+    signals = []
+    for st in stats:
+        max_freq = min(len(freqs) - 1, st[1] + st[3])
+        signals.append((st[0] * 281 / sr, (st[0] + st[2]) * 281 / sr, freqs[st[1]], freqs[max_freq]))
+    return signals, mask, opened, closed, np.array(stats, dtype=np.int64).reshape(-1, 5)
+
+
+def signal_noise(frames, sr, hop_length=281):
+    return signal_noise_stages(frames, sr, hop_length)[0]
+
+
 # ------------------------------------------------------------------- identify_morepork
 MOREPORK_FMIN, MOREPORK_FMAX = 600, 1200
 SLICES_PER_SECOND = 20
