@@ -423,18 +423,32 @@ __global__ void __launch_bounds__(256) seg_minmax_kernel(const float* __restrict
 }
 
 // ---- librosa.power_to_db(S, ref=np.max), top_db = 80, per item ------------------------------
+// explicit _rn intrinsics: no FMA contraction, so the block maximum maps to exactly 0 dB as in numpy;
+// log_spec.max() is refdb - refdb = 0 when ref is the block maximum, so the floor is -top_db.
+__device__ __forceinline__ float db_value(float v, float refdb) {
+    const float d = __fsub_rn(__fmul_rn(10.0f, log10f(fmaxf(1e-10f, v))), refdb);
+    return fmaxf(d, -80.0f);
+}
+// grid = (chunks per item, items): no per-element index arithmetic, 128-bit accesses when aligned
 __global__ void __launch_bounds__(256) power_to_db_kernel(const float* __restrict__ in, float* __restrict__ out,
-                                                          const unsigned* __restrict__ itemmax,
-                                                          long long item_len, long long total) {
-    const float amin = 1e-10f;
-    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-        long long item = i / item_len;
-        float ref = __uint_as_float(itemmax[item]);
-        // explicit _rn intrinsics: no FMA contraction, so the block maximum maps to exactly 0 dB as in numpy
-        float refdb = __fmul_rn(10.0f, log10f(fmaxf(amin, ref)));
-        float v = __fsub_rn(__fmul_rn(10.0f, log10f(fmaxf(amin, in[i]))), refdb);
-        // log_spec.max() is refdb - refdb = 0 when ref is the block maximum, so the floor is -top_db
-        out[i] = fmaxf(v, -80.0f);
+                                                          const unsigned* __restrict__ itemmax, long long item_len) {
+    const long long item = blockIdx.y;
+    const float refdb = __fmul_rn(10.0f, log10f(fmaxf(1e-10f, __uint_as_float(itemmax[item]))));
+    const float* src = in + item * item_len;
+    float* dst = out + item * item_len;
+    const long long stride = (long long)gridDim.x * 256;
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    if ((item_len & 3) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (long long i = t; i < (item_len >> 2); i += stride) {
+            float4 v = s4[i];
+            v.x = db_value(v.x, refdb); v.y = db_value(v.y, refdb);
+            v.z = db_value(v.z, refdb); v.w = db_value(v.w, refdb);
+            d4[i] = v;
+        }
+    } else {
+        for (long long i = t; i < item_len; i += stride) dst[i] = db_value(src[i], refdb);
     }
 }
 
@@ -497,6 +511,19 @@ __global__ void __launch_bounds__(256) mel_project_kernel(const float* __restric
 // host-side launchers (called from cac_api.cu)
 namespace cac {
 
+// items go on grid.y in slices of 65535; each item is covered by ~item_len / (256 * 4 * 4) CTAs
+static void launch_db(const float* in, float* out, const unsigned* itemmax, long long n_items, long long item_len,
+                      cudaStream_t st) {
+    long long bx = (item_len + 256 * 16 - 1) / (256 * 16);
+    if (bx < 1) bx = 1;
+    if (bx > 1024) bx = 1024;
+    for (long long i0 = 0; i0 < n_items; i0 += 65535) {
+        const long long ny = n_items - i0 < 65535 ? n_items - i0 : 65535;
+        power_to_db_kernel<<<dim3((unsigned)bx, (unsigned)ny), 256, 0, st>>>(in + i0 * item_len, out + i0 * item_len,
+                                                                             itemmax + i0, item_len);
+    }
+}
+
 cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st) {
     cudaError_t e = cudaMemcpyToSymbolAsync(c_bands, &bt, sizeof(BandTable), 0, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) return e;
@@ -527,10 +554,8 @@ cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStre
     kern<<<(unsigned)grid, kWarpsPerCta * 32, smem, st>>>(a);
     if (ev1) cudaEventRecord(ev1, st);
     if (db_scale) {
-        const long long item = (long long)a.n_mels * a.n_frames, total = item * a.n_segs;
-        long long blocks = (total + 256 * 8 - 1) / (256 * 8);
-        if (blocks > 148LL * 64) blocks = 148LL * 64;
-        power_to_db_kernel<<<(unsigned)blocks, 256, 0, st>>>(a.out, a.out, a.segmax, item, total);
+        const long long item = (long long)a.n_mels * a.n_frames;
+        launch_db(a.out, a.out, a.segmax, a.n_segs, item, st);
     }
     return cudaGetLastError();
 }
@@ -549,11 +574,7 @@ cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n
 cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, long long item_len, unsigned* work,
                                cudaStream_t st) {
     item_max_kernel<<<(unsigned)n_items, 256, 0, st>>>(in, work, item_len);
-    const long long total = n_items * item_len;
-    long long blocks = (total + 256 * 8 - 1) / (256 * 8);
-    if (blocks > 148LL * 64) blocks = 148LL * 64;
-    if (blocks < 1) blocks = 1;
-    power_to_db_kernel<<<(unsigned)blocks, 256, 0, st>>>(in, out, work, item_len, total);
+    launch_db(in, out, work, n_items, item_len, st);
     return cudaGetLastError();
 }
 
