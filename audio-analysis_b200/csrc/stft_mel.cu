@@ -374,15 +374,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 const float4* pp = reinterpret_cast<const float4*>(pbuf + (live ? mstart[m] : 0));
                 const float4* wg = reinterpret_cast<const float4*>(wts + a.goff[g]) + lane;
                 const int gm4 = a.gmax[g] >> 2;
-                float acc = 0.f;
-                for (int i = 0; i < gm4; ++i) {             // ascending taps; the padding taps add +0
+                // four independent partial sums (one per tap residue mod 4): fixed order, so deterministic,
+                // and the FMA chains of one group overlap instead of serialising on one accumulator
+                float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+#pragma unroll 2
+                for (int i = 0; i < gm4; ++i) {             // the padding taps add +0
                     const float4 w = wg[i * 32];
                     const float4 p = pp[i];
-                    acc = fmaf(w.x, p.x, acc);
-                    acc = fmaf(w.y, p.y, acc);
-                    acc = fmaf(w.z, p.z, acc);
-                    acc = fmaf(w.w, p.w, acc);
+                    acc0 = fmaf(w.x, p.x, acc0);
+                    acc1 = fmaf(w.y, p.y, acc1);
+                    acc2 = fmaf(w.z, p.z, acc2);
+                    acc3 = fmaf(w.w, p.w, acc3);
                 }
+                const float acc = (acc0 + acc1) + (acc2 + acc3);
                 if (live) {
                     outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
                     vmax = fmaxf(vmax, acc);
