@@ -63,3 +63,46 @@ def _projection_plan(sr, n_fft, hop_length, n_mels, fmin, fmax, break_freq, powe
     w = _mel_f_cached(sr, n_mels, fmin, fmax, n_fft, break_freq)
     return engine.FeaturePlan(w, sr, n_fft, hop_length, n_mels, segment_samples=n_fft, power=power,
                               db_scale=False, normalize=False)
+
+
+# ---- librosa's own (Slaney) filterbank: the htk=False branch of get_spect --------------------------
+def _slaney_hz_to_mel(f):
+    """librosa.hz_to_mel(htk=False): linear below 1 kHz (200/3 Hz per mel), logarithmic above."""
+    f = np.asarray(f, dtype=np.float64)
+    f_sp = 200.0 / 3
+    mels = f / f_sp
+    min_log_hz = 1000.0
+    min_log_mel = min_log_hz / f_sp
+    logstep = np.log(6.4) / 27.0
+    return np.where(f >= min_log_hz, min_log_mel + np.log(np.maximum(f, 1e-300) / min_log_hz) / logstep, mels)
+
+
+def _slaney_mel_to_hz(m):
+    m = np.asarray(m, dtype=np.float64)
+    f_sp = 200.0 / 3
+    min_log_hz = 1000.0
+    min_log_mel = min_log_hz / f_sp
+    logstep = np.log(6.4) / 27.0
+    return np.where(m >= min_log_mel, min_log_hz * np.exp(logstep * (m - min_log_mel)), f_sp * m)
+
+
+@functools.lru_cache(maxsize=16)
+def _slaney_mel_f_cached(sr, n_fft, n_mels, fmin, fmax):
+    """librosa.filters.mel(sr, n_fft, n_mels, fmin, fmax, htk=False, norm="slaney") as reached through
+    librosa.feature.melspectrogram at src/identify_tracks.py:230-238 (librosa ~= 0.11; restated from its
+    documented algorithm - librosa itself is not installable here, so this boundary is unpinned)."""
+    bin_hz = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
+    pts = _slaney_mel_to_hz(np.linspace(_slaney_hz_to_mel(fmin), _slaney_hz_to_mel(fmax), n_mels + 2))
+    width = np.diff(pts)
+    dist = pts[:, None] - bin_hz[None, :]
+    rising = -dist[:n_mels] / width[:n_mels, None]
+    falling = dist[2:n_mels + 2] / width[1:n_mels + 1, None]
+    tri = np.maximum(0, np.minimum(rising, falling)).astype(np.float32)
+    area = 2.0 / (pts[2:n_mels + 2] - pts[:n_mels])
+    tri = (tri.astype(np.float64) * area[:, None]).astype(np.float32)
+    tri.setflags(write=False)
+    return tri
+
+
+def slaney_mel_f(sr, n_fft, n_mels, fmin, fmax):
+    return np.array(_slaney_mel_f_cached(sr, int(n_fft), int(n_mels), fmin, fmax))

@@ -28,8 +28,12 @@ class Signal:
 
 @functools.lru_cache(maxsize=16)
 def _plan(sr, n_fft, hop_length, n_mels, fmin, fmax, mel_break, segment_samples, power, db_scale, normalize):
+    """mel_break None selects librosa's own Slaney filterbank (get_spect's htk=False branch)."""
     from . import engine
-    w = custommel._mel_f_cached(sr, n_mels, fmin, fmax, n_fft, mel_break)
+    if mel_break is None:
+        w = custommel._slaney_mel_f_cached(sr, n_fft, n_mels, fmin, fmax)
+    else:
+        w = custommel._mel_f_cached(sr, n_mels, fmin, fmax, n_fft, mel_break)
     return engine.FeaturePlan(w, sr, n_fft, hop_length, n_mels, segment_samples, power=power,
                               db_scale=db_scale, normalize=normalize)
 
@@ -99,8 +103,9 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
     """Same signature and return structure as src/identify_tracks.py:65-199: one list per
     track (empty for out-of-band tracks), each holding [n_mels, frames, channels] arrays."""
     logging.debug("Loading samples with length %s stride %s hop length %s", segment_length, stride, hop_length)
-    if use_mfcc or not htk:
-        raise NotImplementedError("use_mfcc / htk=False branches (librosa.feature) are not built")
+    if use_mfcc:
+        raise NotImplementedError("use_mfcc: the reference branch (src/identify_tracks.py:269-280) cannot run "
+                                  "(tf.image.resize_with_pad on a 2-D mfcc with *mel.shape); not built")
     if filter_freqs or filter_below:
         raise NotImplementedError("Butterworth pre-filter is a host pre-step outside this path")
     frames = np.ascontiguousarray(frames, dtype=np.float32)
@@ -108,6 +113,8 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
                                        pad_short_tracks)
     if len(segs) == 0:
         return [[] for _ in counts]
+    if not htk:     # librosa.feature.melspectrogram(fmin=50, fmax=11000): Slaney mel, power 2 (:229-238)
+        fmin, fmax, power, mel_break = 50, 11000, 2, None
     plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break,
                  int(sr * segment_length), int(power), bool(db_scale), bool(normalize))
     block = _finish(plan.run_host(frames, segs), mean_sub, channels)
@@ -128,11 +135,14 @@ def get_spect(data, sr, hop_length, mean_sub, use_mfcc, mel_break, htk, n_mels, 
               db_scale, channels=1, pass_freqs=None):
     """src/identify_tracks.py:212-288 for one already-normalised segment."""
     from .engine import SEGMENT_DTYPE
-    if use_mfcc or not htk:
-        raise NotImplementedError("use_mfcc / htk=False branches (librosa.feature) are not built")
+    if use_mfcc:
+        raise NotImplementedError("use_mfcc: the reference branch cannot run as written; not built")
     data = np.ascontiguousarray(data, dtype=np.float32)
-    plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), 50 if fmin is None else fmin,
-                 11000 if fmin is None else fmax, mel_break, len(data), int(power), bool(db_scale), False)
+    if not htk:     # librosa.feature.melspectrogram(fmin=50, fmax=11000): Slaney mel, power 2 (:229-238)
+        plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), 50, 11000, None, len(data), 2, bool(db_scale), False)
+    else:
+        plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), 50 if fmin is None else fmin,
+                     11000 if fmin is None else fmax, mel_break, len(data), int(power), bool(db_scale), False)
     seg = np.array([(0, len(data), 0)], dtype=SEGMENT_DTYPE)
     return _finish(plan.run_host(data, seg), mean_sub, channels)[0]
 
@@ -192,8 +202,9 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
 SIGNAL_WIDTH = 0.25   # src/identify_tracks.py:21
 
 
-def signal_noise(frames, sr, hop_length=281):
-    """src/identify_tracks.py:650-706: candidate track signals of a recording.  STFT magnitude,
+def signal_noise(frames, sr, hop_length=281, signal_cls=None):
+    """src/identify_tracks.py:650-706: candidate track signals of a recording (`signal_cls`: the class to
+    build, e.g. the reference's own Signal with its merge helpers; default: this module's Signal).  STFT magnitude,
     medians, threshold, morphology and connected components run on the GPU
     (signal_noise_spectrogram + engine.signal_components); the handful of component boxes comes back
     to the host, where the reference's filter (:689-691) and time / frequency conversion (:697-704,
@@ -215,5 +226,5 @@ def signal_noise(frames, sr, hop_length=281):
         if not (w > min_width and h > min_height):
             continue
         max_freq = min(len(freqs) - 1, y + h)
-        signals.append(Signal(x * 281 / sr, (x + w) * 281 / sr, freqs[y], freqs[max_freq]))
+        signals.append((signal_cls or Signal)(x * 281 / sr, (x + w) * 281 / sr, freqs[y], freqs[max_freq]))
     return signals

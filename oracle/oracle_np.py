@@ -89,6 +89,26 @@ def mel_f(sr, n_mels, fmin, fmax, n_fft, break_freq):
     return weights
 
 
+def slaney_mel_filterbank(sr, n_fft, n_mels, fmin, fmax):
+    """librosa.filters.mel(htk=False, norm="slaney") as used by librosa.feature.melspectrogram
+    (src/identify_tracks.py:230-238); Slaney scale: 200/3 Hz per mel below 1 kHz, log(6.4)/27 per mel above."""
+    f_sp, min_log_hz, logstep = 200.0 / 3, 1000.0, np.log(6.4) / 27.0
+
+    def h2m(f):
+        return f / f_sp if f < min_log_hz else min_log_hz / f_sp + np.log(f / min_log_hz) / logstep
+
+    mels = np.linspace(h2m(float(fmin)), h2m(float(fmax)), n_mels + 2)
+    pts = np.where(mels >= min_log_hz / f_sp, min_log_hz * np.exp(logstep * (mels - min_log_hz / f_sp)), f_sp * mels)
+    weights = np.zeros((n_mels, 1 + n_fft // 2), dtype=np.float32)
+    fftfreqs = fft_frequencies(sr, n_fft)
+    fdiff = np.diff(pts)
+    ramps = np.subtract.outer(pts, fftfreqs)
+    for i in range(n_mels):
+        weights[i] = np.maximum(0, np.minimum(-ramps[i] / fdiff[i], ramps[i + 2] / fdiff[i + 1]))
+    weights *= (2.0 / (pts[2:n_mels + 2] - pts[:n_mels]))[:, np.newaxis]
+    return weights
+
+
 def mel_spec(stft_mag, sr, n_fft, hop_length, n_mels, fmin, fmax, break_freq=1750, power=2):
     """src/custommel.py:59-63."""
     magnitude = np.abs(stft_mag) ** power
@@ -121,12 +141,16 @@ def normalize_data(x):
 
 def get_spect(data, sr, hop_length, mean_sub, use_mfcc, mel_break, htk, n_mels, fmin, fmax,
               n_fft, power, db_scale, channels=1):
-    """src/identify_tracks.py:212-288, htk=True and use_mfcc=False branches."""
-    assert htk and not use_mfcc, "only the custom-mel branch is restated"
+    """src/identify_tracks.py:212-288, use_mfcc=False.  htk=False = librosa.feature.melspectrogram with
+    librosa's own Slaney filterbank (restated from librosa 0.11's documented algorithm: unpinned)."""
+    assert not use_mfcc, "the use_mfcc branch cannot run in the reference either"
     spectogram = np.abs(stft(data, n_fft, hop_length))
-    mel = mel_spec(spectogram, sr, n_fft, hop_length, n_mels,
-                   50 if fmin is None else fmin, 11000 if fmin is None else fmax,
-                   mel_break, power=power)
+    if not htk:
+        mel = slaney_mel_filterbank(sr, n_fft, n_mels, 50, 11000).dot(spectogram ** 2.0)
+    else:
+        mel = mel_spec(spectogram, sr, n_fft, hop_length, n_mels,
+                       50 if fmin is None else fmin, 11000 if fmin is None else fmax,
+                       mel_break, power=power)
     if db_scale:
         mel = power_to_db(mel, ref=np.max)
     mel = np.expand_dims(mel, axis=2)

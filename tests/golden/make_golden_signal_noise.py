@@ -30,3 +30,18 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def slaney():
+    """tests/golden/get_spect_slaney.npz: the reference's get_spect(htk=False) under the librosa stand-in."""
+    from oracle import oracle_np as O
+    it = rl.load("identify_tracks")
+    rec = synth.recording(1234, seconds=12.0)
+    x = O.normalize_data(rec[48000:48000 + 144000])
+    ref = np.asarray(it.get_spect(x, 48000, 281, False, False, 1750, False, 160, 50, 11000, 4096, 2, True))
+    np.savez_compressed(os.path.join(OUT, "get_spect_slaney.npz"), seed=1234, seg_start=48000,
+                        s1_db=ref[:, :, 0].astype(np.float32))
+
+
+if __name__ == "__main__" and "slaney" in sys.argv:
+    slaney()

@@ -158,3 +158,21 @@ def test_error_paths(engine):
     good = engine.FeaturePlan(custommel.mel_f(48000, 160, 50, 11000, 4096, 1750), 48000, 4096, 281, 160, 144000)
     with pytest.raises(engine.CacError):   # descriptor past the end of the pcm buffer
         good.run_host(np.zeros(1000, np.float32), np.array([(0, 144000, 0)], dtype=engine.SEGMENT_DTYPE))
+
+
+def test_htk_false_slaney_branch(engine, golden):
+    """get_spect(htk=False) = librosa.feature.melspectrogram (Slaney filterbank, fmin 50, fmax 11000, power 2)."""
+    from audio_analysis_b200 import identify_tracks as T
+    g = golden("get_spect_slaney")
+    rec = synth.recording(int(g["seed"]), seconds=12.0)
+    s0 = int(g["seg_start"])
+    x = O.normalize_data(rec[s0:s0 + 144000])
+    got = T.get_spect(x, 48000, 281, False, False, 1750, False, 160, 50, 11000, 4096, 2, True)
+    assert got.shape == (160, 513, 1)
+    assert np.abs(got[:, :, 0] - g["s1_db"]).max() <= 1e-2
+    tracks = [(0.0, 6.0, 0, 24000)]
+    a = T.load_samples(rec[:288000], 48000, [T.Signal(*t) for t in tracks], 3.0, 1.5, htk=False, db_scale=True, **S1)
+    b = O.load_samples(rec[:288000], 48000, [O.Signal(*t) for t in tracks], 3.0, 1.5, htk=False, db_scale=True, **S1)
+    assert len(a[0]) == len(b[0]) == 3
+    for u, v in zip(a[0], b[0]):
+        assert np.abs(u - v).max() <= 1e-2

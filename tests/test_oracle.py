@@ -147,3 +147,22 @@ def test_stft_standin_matches_torch():
                    center=True, pad_mode="constant", return_complex=True).abs().numpy()
     assert ref.shape == t.shape == (2049, 513)
     assert np.abs(ref - t).max() < 2e-3 * max(1.0, ref.max() / 100)
+
+
+def test_slaney_branch_matches_reference_under_stub(golden):
+    g = golden("get_spect_slaney")
+    rec = synth.recording(int(g["seed"]), seconds=12.0)
+    s0 = int(g["seg_start"])
+    x = O.normalize_data(rec[s0:s0 + 144000])
+    mine = O.get_spect(x, 48000, 281, False, False, 1750, False, 160, 50, 11000, 4096, 2, True)
+    assert np.abs(mine[:, :, 0] - g["s1_db"]).max() <= 1e-4
+    from audio_analysis_b200 import custommel
+    assert np.array_equal(custommel.slaney_mel_f(48000, 4096, 160, 50, 11000), O.slaney_mel_filterbank(48000, 4096, 160, 50, 11000))
+
+
+def test_signal_noise_oracle_equals_reference_fixture(golden):
+    g = golden("signal_noise")
+    for name in "abc":
+        rec = synth.recording(int(g[name + "_seed"]), seconds=float(g[name + "_seconds"]))
+        sig = O.signal_noise(rec, 48000)
+        assert np.array_equal(np.array(sig, dtype=np.float64).reshape(-1, 4), g[name + "_signals"])
