@@ -113,6 +113,7 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
         a.n_taps = (int)plan->mb.wpad.size();
         a.pbuf_len = plan->mb.pbuf_len;
         a.n_mels = p.n_mels;
+        a.frames_per_stage = fs;
         if (feat_smem_bytes(a) <= 227 * 1024) { plan->frames_per_stage = fs; plan->stage_half = half; break; }
     }
     if (!plan->frames_per_stage && plan->fused_unsupported.empty())

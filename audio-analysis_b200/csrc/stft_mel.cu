@@ -214,9 +214,10 @@ struct FeatSmem {
     int wts;           // padded tap-major band weights (FeatArgs::wpad)
     int bands;         // int: mstart[n_mels]
     int ltab;          // 32 x 32
+    int otile;         // n_mels x (frames_per_stage + 1): this stage's mel values, flushed as row segments
     int total;
 };
-__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps, int n_mels) {
+__host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps, int n_mels, int frames_per_stage) {
     FeatSmem L;
     int o = 0;
     L.raw = o; o += 2 * stage_half;
@@ -226,6 +227,7 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
     L.bands = o; o += n_mels;
     o = (o + 31) / 32 * 32;
     L.ltab = o; o += 32 * 32;
+    L.otile = o; o += n_mels * (frames_per_stage + 1);
     L.total = o;
     return L;
 }
@@ -237,13 +239,15 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
 template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
-    const FeatSmem L = feat_smem_layout(a.stage_half, a.n_taps, a.n_mels);
+    const FeatSmem L = feat_smem_layout(a.stage_half, a.n_taps, a.n_mels, a.frames_per_stage);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* ex = smem + L.ex + warp * kExFloats;
     float* pbuf = ex;   // the power spectrum reuses the warp's exchange buffer once pass 2 has read it
     float* wts = smem + L.wts;
     int* mstart = reinterpret_cast<int*>(smem + L.bands);
     float* ltab = smem + L.ltab;
+    float* otile = smem + L.otile;
+    const int tstride = a.frames_per_stage + 1;       // odd row stride: conflict-free both ways
 
     // ---- one-time tables ------------------------------------------------------------------------
     for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
@@ -299,9 +303,34 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         cp_async_commit();
     };
 
-    long long q = blockIdx.x;
-    if (q < n_stages) issue_stage(q);
-    for (; q < n_stages; q += gridDim.x) {
+    // The warps park a stage's mel values in otile ([mel][frame]); the whole CTA then writes every mel row's
+    // frames_per_stage consecutive frames as one contiguous run (full 32-byte sectors instead of 4-byte
+    // stores scattered over n_mels rows: no read-modify-write fills in L2 / HBM).
+    auto flush_tile = [&](long long qp) {
+        const long long seg = qp / a.stages_per_seg;
+        const int f0 = (int)(qp - seg * a.stages_per_seg) * a.frames_per_stage;
+        const int nfs = min(a.frames_per_stage, a.n_frames - f0);
+        float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames + f0;
+        constexpr int kThreads = kWarpsPerCta * 32;
+        if (kThreads % nfs == 0) {               // full stages (24 frames): a fixed (row, frame) walk, no divisions
+            const int rows_per_iter = kThreads / nfs;
+            int m = tid / nfs;
+            const int f = tid - m * nfs;
+            for (; m < a.n_mels; m += rows_per_iter) outseg[(size_t)m * a.n_frames + f] = otile[m * tstride + f];
+        } else {
+            for (int t = tid; t < a.n_mels * nfs; t += kThreads) {
+                const int m = t / nfs, f = t - m * nfs;
+                outseg[(size_t)m * a.n_frames + f] = otile[m * tstride + f];
+            }
+        }
+    };
+
+    // blocked distribution: every CTA owns a contiguous run of stages, so the samples two consecutive
+    // stages (and the two 50 %-overlapping segments) share are re-read by the SAME CTA a moment later
+    const long long q_begin = n_stages * blockIdx.x / gridDim.x, q_end = n_stages * (blockIdx.x + 1) / gridDim.x;
+    long long q = q_begin, q_prev = -1;
+    if (q < q_end) issue_stage(q);
+    for (; q < q_end; ++q) {
         const long long seg = q / a.stages_per_seg;
         const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
@@ -309,6 +338,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
 
         cp_async_wait_all();
         __syncthreads();                       // raw has stage q; every warp is done with the previous stage
+        if (q_prev >= 0) flush_tile(q_prev);   // (the barrier after the normalise pass orders this against new tile writes)
         {   // raw -> normalised even/odd planes (normalize_data, exact float32 op order)
             const cac_segment sd = a.segs[seg];
             const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
@@ -356,10 +386,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             }
         }
         __syncthreads();                       // planes ready; raw is free again
-        if (q + gridDim.x < n_stages) issue_stage(q + gridDim.x);
+        if (q + 1 < q_end) issue_stage(q + 1);
 
         float vmax = 0.f;
-        float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames;
 #pragma unroll 1
         for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
             fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt, a.kmin, a.nbins);
@@ -388,7 +417,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 }
                 const float acc = (acc0 + acc1) + (acc2 + acc3);
                 if (live) {
-                    outseg[(size_t)m * a.n_frames + f0 + fi] = acc;
+                    otile[m * tstride + fi] = acc;
                     vmax = fmaxf(vmax, acc);
                 }
             }
@@ -396,7 +425,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         }
         vmax = warp_max(vmax);
         if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
+        q_prev = q;
     }
+    __syncthreads();
+    if (q_prev >= 0) flush_tile(q_prev);
 }
 
 // ---- per-segment min / max of the zero-padded segment (normalize_data's reductions) ---------
@@ -535,7 +567,7 @@ cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, 
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
-    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.n_taps, a.n_mels).total;
+    return sizeof(float) * (size_t)feat_smem_layout(a.stage_half, a.n_taps, a.n_mels, a.frames_per_stage).total;
 }
 
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
