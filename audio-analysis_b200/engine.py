@@ -80,8 +80,9 @@ lib.cac_signal_components.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _
 lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
+lib.cac_spect_tail_run.argtypes = [_vp, _i64, _i32, _i32, _i32, _vp, _vp]
 
-EXPORTS = ["cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_spect_tail_run", "cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
@@ -407,6 +408,22 @@ def magtransform(x, a, device=0):
     with torch.cuda.device(dev):
         check(lib.cac_magtransform_run(t.data_ptr(), out.data_ptr(), t.numel(), float(a), _stream_ptr(torch)))
     return out.cpu().numpy() if was_np else out
+
+
+def spect_tail(block, mean_sub=False, channels=1):
+    """get_spect's tail on a CUDA float32 [n, n_mels, frames] block: returns [n, n_mels, frames, channels]
+    (mean over frames subtracted per mel row when mean_sub), still on the device."""
+    torch = _torch()
+    assert block.is_cuda and block.dtype == torch.float32 and block.is_contiguous() and block.dim() == 3
+    n, n_mels, frames = block.shape
+    channels = int(channels)
+    if not mean_sub and channels == 1:
+        return block.unsqueeze(-1)
+    out = block if channels == 1 else torch.empty((n, n_mels, frames, channels), dtype=torch.float32, device=block.device)
+    with torch.cuda.device(block.device):
+        check(lib.cac_spect_tail_run(block.data_ptr(), n * n_mels, frames, int(bool(mean_sub)), channels,
+                                     out.data_ptr(), _stream_ptr(torch)))
+    return out.view(n, n_mels, frames, channels)
 
 
 class pinned:

@@ -125,6 +125,36 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
     return out
 
 
+def load_samples_device(frames, sr, tracks, segment_length, stride, hop_length=281, mean_sub=False,
+                        mel_break=1000, htk=True, n_mels=160, fmin=50, fmax=11000, channels=1, power=2,
+                        db_scale=False, normalize=True, n_fft=4096, pad_short_tracks=False, device=0):
+    """load_samples for a classifier that lives on the GPU: `frames` is a numpy array or a
+    CUDA float32 tensor; returns one CUDA tensor [n_segments, n_mels, frames, channels] per track (views of
+    one block; a [0, ...] tensor for out-of-band tracks), i.e. what `np.array(d)` builds at
+    src/identify_tracks.py:544 - nothing is copied back to the host.  mean_sub / channels (and classify's
+    efficientnet x3 repeat, :539-540 = channels 3) run in cac_spect_tail_run."""
+    import torch
+    from . import engine
+    dev = torch.device("cuda", device)
+    if isinstance(frames, np.ndarray):
+        frames = torch.from_numpy(np.ascontiguousarray(frames, dtype=np.float32)).to(dev)
+    assert frames.is_cuda and frames.dtype == torch.float32 and frames.dim() == 1 and frames.is_contiguous()
+    segs, counts = segment_descriptors(frames.numel(), sr, tracks, segment_length, stride, fmin, fmax, pad_short_tracks)
+    if not htk:
+        fmin, fmax, power, mel_break = 50, 11000, 2, None
+    plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break,
+                 int(sr * segment_length), int(power), bool(db_scale), bool(normalize))
+    if len(segs) == 0:
+        empty = torch.empty((0, int(n_mels), plan.n_frames, int(channels)), dtype=torch.float32, device=dev)
+        return [empty for _ in counts]
+    block = engine.spect_tail(plan.run(frames, segs), mean_sub, channels)
+    out, k = [], 0
+    for c in counts:
+        out.append(block[k:k + c])
+        k += c
+    return out
+
+
 def normalize_data(x):
     """src/identify_tracks.py:202-209 on the GPU (bit-exact float32 op order)."""
     from . import engine

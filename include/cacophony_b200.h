@@ -193,6 +193,14 @@ int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32
                           int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
                           uint8_t* d_stage_masks, void* stream);
 
+/* get_spect's tail (src/identify_tracks.py:267, 282-287) for the classifier hand-off on the device:
+ * d_in [n_rows][n_frames] (n_rows = segments x mel rows) -> d_out [n_rows][n_frames][channels] =
+ * (value - mean over the row's frames, when mean_sub) repeated `channels` times (tf.expand_dims /
+ * tf.reduce_mean(axis=1) / tf.repeat(axis=2); classify's efficientnet x3 repeat, :539-540, is channels = 3).
+ * In place (d_out == d_in) is allowed when channels == 1. */
+int cac_spect_tail_run(const float* d_in, int64_t n_rows, int32_t n_frames, int32_t mean_sub, int32_t channels,
+                       float* d_out, void* stream);
+
 /* MagTransform.call (src/magtransform.py:17-19, src/magtransformv2.py:19-21): d_out = d_in ** sigmoid(a),
  * elementwise float32 (in place allowed); `a` is the layer's learned scalar (v1 init 0.0, v2 init -1.0). */
 int cac_magtransform_run(const float* d_in, float* d_out, int64_t n, float a, void* stream);

@@ -176,3 +176,34 @@ def test_htk_false_slaney_branch(engine, golden):
     assert len(a[0]) == len(b[0]) == 3
     for u, v in zip(a[0], b[0]):
         assert np.abs(u - v).max() <= 1e-2
+
+
+def test_load_samples_device_tail_matches_host_path(engine):
+    """Classifier hand-off on the device: [n_seg, n_mels, frames, channels] CUDA tensors per track equal the
+    host path (load_samples) - bitwise without mean_sub, within float32 rounding of the row mean with it."""
+    import torch
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(41, seconds=9.0)
+    tracks = [T.Signal(0.0, 9.0, 0, 24000), T.Signal(1.0, 2.0, 13000, 15000), T.Signal(2.5, 7.1, 500, 9000)]
+    kw = dict(segment_length=3.0, stride=1.5, db_scale=True, **S1)
+    for mean_sub, channels in ((False, 1), (True, 1), (False, 3), (True, 3)):
+        np.random.seed(5)
+        host = T.load_samples(rec, 48000, tracks, mean_sub=mean_sub, channels=channels, **kw)
+        np.random.seed(5)
+        dev = T.load_samples_device(torch.from_numpy(rec).cuda(), 48000, tracks, mean_sub=mean_sub, channels=channels, **kw)
+        assert len(dev) == len(host) == 3 and dev[1].shape[0] == 0 and len(host[1]) == 0
+        for d, h in zip(dev, host):
+            assert d.is_cuda and d.shape[0] == len(h)
+            if len(h) == 0:
+                continue
+            hh = np.stack(h)
+            assert tuple(d.shape) == hh.shape and d.shape[3] == channels
+            if mean_sub:
+                assert np.abs(d.cpu().numpy() - hh).max() <= 1e-5
+                assert float(d.double().mean(dim=2).abs().max()) <= 2e-5
+            else:
+                assert np.array_equal(d.cpu().numpy(), hh)
+    ref = O.load_samples(rec, 48000, [O.Signal(0.0, 9.0, 0, 24000)], 3.0, 1.5, db_scale=True, mean_sub=True, channels=3, **S1)
+    np.random.seed(5)
+    got = T.load_samples_device(rec, 48000, [T.Signal(0.0, 9.0, 0, 24000)], mean_sub=True, channels=3, **kw)[0]
+    assert np.abs(got.cpu().numpy() - np.stack(ref[0])).max() <= 1e-2
