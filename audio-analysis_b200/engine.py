@@ -81,8 +81,13 @@ lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
 lib.cac_spect_tail_run.argtypes = [_vp, _i64, _i32, _i32, _i32, _vp, _vp]
+lib.cac_resample_plan_create.argtypes = [_i32, _i32, _vp, _i32, _i32, ctypes.c_int, ctypes.POINTER(_vp)]
+lib.cac_resample_plan_destroy.argtypes = [_vp]
+lib.cac_resample_out_len.argtypes = [_vp, _i64]
+lib.cac_resample_out_len.restype = _i64
+lib.cac_resample_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 
-EXPORTS = ["cac_spect_tail_run", "cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
@@ -408,6 +413,46 @@ def magtransform(x, a, device=0):
     with torch.cuda.device(dev):
         check(lib.cac_magtransform_run(t.data_ptr(), out.data_ptr(), t.numel(), float(a), _stream_ptr(torch)))
     return out.cpu().numpy() if was_np else out
+
+
+class ResamplePlan:
+    """cac_resample_plan: polyphase FIR resampling by up / down with the caller's (padded) filter."""
+
+    def __init__(self, up, down, taps, n_pre_remove, device=0):
+        taps = np.ascontiguousarray(taps, dtype=np.float32)
+        self.up, self.down, self.device = int(up), int(down), int(device)
+        self._h = _vp()
+        check(lib.cac_resample_plan_create(self.up, self.down, taps.ctypes.data_as(_vp), len(taps), int(n_pre_remove),
+                                           self.device, ctypes.byref(self._h)))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.cac_resample_plan_destroy(self._h)
+            self._h = None
+
+    def out_len(self, n_in):
+        return int(lib.cac_resample_out_len(self._h, int(n_in)))
+
+    def run(self, pcm, in_offset, in_samples, out=None, out_offset=None):
+        """Resample items of the flat CUDA float32 tensor `pcm`; returns (out, out_offset [n + 1] int64):
+        item i occupies out[out_offset[i] : out_offset[i + 1]] unless explicit out_offset are given."""
+        torch = _torch()
+        off = np.ascontiguousarray(in_offset, dtype=np.int64)
+        ns = np.ascontiguousarray(in_samples, dtype=np.int64)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        assert off.shape == ns.shape and (off + ns <= pcm.numel()).all()
+        lens = np.array([self.out_len(v) for v in ns], dtype=np.int64)
+        if out_offset is None:
+            out_offset = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        oo = np.ascontiguousarray(out_offset, dtype=np.int64)
+        need = int((oo[:len(lens)] + lens).max()) if len(lens) else 0
+        if out is None:
+            out = torch.empty((need,), dtype=torch.float32, device=pcm.device)
+        assert out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and out.numel() >= need
+        with torch.cuda.device(pcm.device):
+            check(lib.cac_resample_run(self._h, pcm.data_ptr(), off.ctypes.data_as(_vp), ns.ctypes.data_as(_vp), len(off),
+                                       out.data_ptr(), oo.ctypes.data_as(_vp), _stream_ptr(torch)))
+        return out, oo
 
 
 def spect_tail(block, mean_sub=False, channels=1):

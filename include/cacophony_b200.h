@@ -193,6 +193,22 @@ int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32
                           int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
                           uint8_t* d_stage_masks, void* stream);
 
+/* Rational-rate resampling front-end: replaces `ffmpeg -ar 16000` in front of the Cacophony
+ * Index (src/common.py:76-79) and librosa.resample to 48 kHz (src/identify_tracks.py:55-57).  The filter is the
+ * caller's: `h_taps` is the zero-padded polyphase prototype and `n_pre_remove` the number of leading outputs to
+ * drop, exactly the quantities scipy.signal.resample_poly derives (audio-analysis_b200/resample.py builds them);
+ * y[m] = sum_k h[k] xu[(m + n_pre_remove) down - k], xu = x zero-stuffed by `up`, zeros outside the item.
+ * Every item i reads h_in_samples[i] samples at d_in + h_in_offset[i] and writes cac_resample_out_len() samples
+ * at d_out + h_out_offset[i].  No allocation besides the item table, no synchronisation. */
+typedef struct cac_resample_plan cac_resample_plan;
+int cac_resample_plan_create(int32_t up, int32_t down, const float* h_taps, int32_t n_taps, int32_t n_pre_remove,
+                             int device, cac_resample_plan** out);
+int cac_resample_plan_destroy(cac_resample_plan* plan);
+int64_t cac_resample_out_len(const cac_resample_plan* plan, int64_t n_in);
+int cac_resample_run(cac_resample_plan* plan, const float* d_in, const int64_t* h_in_offset,
+                     const int64_t* h_in_samples, int64_t n_items, float* d_out, const int64_t* h_out_offset,
+                     void* stream);
+
 /* get_spect's tail (src/identify_tracks.py:267, 282-287) for the classifier hand-off on the device:
  * d_in [n_rows][n_frames] (n_rows = segments x mel rows) -> d_out [n_rows][n_frames][channels] =
  * (value - mean over the row's frames, when mean_sub) repeated `channels` times (tf.expand_dims /

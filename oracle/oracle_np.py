@@ -451,3 +451,13 @@ def magtransform(x, a):
     a = np.float32(a)
     p = np.float32(1.0) / (np.float32(1.0) + np.exp(-a, dtype=np.float32))
     return np.power(np.asarray(x, dtype=np.float32), p).astype(np.float32)
+
+
+# --------------------------------------------------------------------- resampling front-end
+def resample_poly(x, up, down):
+    """The resampling front-end's stated filter (the reference itself uses ffmpeg
+    -ar 16000, src/common.py:76-79, and librosa.resample, src/identify_tracks.py:55-57, neither of
+    which exists here): scipy.signal.resample_poly with its default Kaiser(5.0) design and zero padding."""
+    import scipy.signal
+    return scipy.signal.resample_poly(np.asarray(x, dtype=np.float32), up, down)
+
