@@ -96,7 +96,7 @@ __host__ __device__ inline Smem48 smem48_layout(int rows, int n_mels, int n_taps
     L.lt = o; o += kSpec4800LtabRows * 32 * 8;
     L.rt = o; o += ((kSpec4800Rounds * 8 + 15) / 16) * 16;
     L.wts = o; o += ((n_mels ? n_taps : 0) * 4 + 15) / 16 * 16;
-    L.mstart = o; o += (n_mels * 4 + 15) / 16 * 16;
+    L.mstart = o; o += (n_mels + 31) / 32 * 32 * 4;
     L.ex = o; o += kWarps48 * rows * kExStride48 * 8;
     L.pbuf = o; o += kWarps48 * (n_mels ? pbuf_len : 0) * 4;
     L.total = o;
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
     for (int i = tid; i < kSpec4800Rounds; i += kWarps48 * 32) rtab[i] = a.rtab[i];
     if (a.n_mels) {
         for (int i = tid; i < a.n_taps; i += kWarps48 * 32) wts[i] = a.wpad[i];
-        for (int i = tid; i < a.n_mels; i += kWarps48 * 32) mstart[i] = a.mstart[i];
+        for (int i = tid; i < a.n_groups * 32; i += kWarps48 * 32) mstart[i] = a.mstart[i];
     }
     __syncthreads();
     const float2* lt = ltab + lane;
@@ -202,9 +202,10 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
             float* oitem = a.out + (size_t)fbase * a.n_mels;
 #pragma unroll 1
             for (int gidx = 0; gidx < a.n_groups; ++gidx) {
-                const int m = gidx * 32 + lane;
-                const bool live = m < a.n_mels;
-                const float4* pp = reinterpret_cast<const float4*>(pbuf + (live ? mstart[m] : 0));
+                const int slot = mstart[gidx * 32 + lane];   // (band start) | row << 16, mel_bands.h
+                const int m = (int)((unsigned)slot >> 16);
+                const bool live = m != 0xFFFF;
+                const float4* pp = reinterpret_cast<const float4*>(pbuf + (slot & 0xFFFF));
                 const float4* wg = reinterpret_cast<const float4*>(wts + a.goff[gidx]) + lane;
                 const int gm4 = a.gmax_taps[gidx] >> 2;
                 float acc = 0.f;

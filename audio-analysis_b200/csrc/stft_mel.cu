@@ -212,7 +212,7 @@ struct FeatSmem {
     int stage;         // 2 planes (even / odd samples) of stage_half floats: normalised samples of this stage
     int ex;            // 8 warps x kExFloats
     int wts;           // padded tap-major band weights (FeatArgs::wpad)
-    int bands;         // int: mstart[n_mels]
+    int bands;         // int: slot table mstart[n_groups * 32] (mel_bands.h)
     int ltab;          // 32 x 32
     int otile;         // n_mels x (frames_per_stage + 1): this stage's mel values, flushed as row segments
     int total;
@@ -224,7 +224,7 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
     L.stage = o; o += 2 * stage_half;
     L.ex = o; o += kWarpsPerCta * kExFloats;
     L.wts = o; o += (n_taps + 3) / 4 * 4;
-    L.bands = o; o += n_mels;
+    L.bands = o; o += (n_mels + 31) / 32 * 32;
     o = (o + 31) / 32 * 32;
     L.ltab = o; o += 32 * 32;
     L.otile = o; o += n_mels * (frames_per_stage + 1);
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
 
     // ---- one-time tables ------------------------------------------------------------------------
     for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
-    for (int m = tid; m < a.n_mels; m += kWarpsPerCta * 32) mstart[m] = a.mstart[m];
+    for (int m = tid; m < a.n_groups * 32; m += kWarpsPerCta * 32) mstart[m] = a.mstart[m];
     if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
@@ -397,10 +397,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
 #pragma unroll 1
             for (int g = 0; g < a.n_groups; ++g) {
-                const int m = g * 32 + lane;
-                const bool live = m < a.n_mels;
-                // band start rounded down to 4 bins (zero weights in front): both loads are 128-bit
-                const float4* pp = reinterpret_cast<const float4*>(pbuf + (live ? mstart[m] : 0));
+                const int slot = mstart[g * 32 + lane];      // (band start rounded down to 4 bins) | row << 16
+                const int m = (int)((unsigned)slot >> 16);
+                const bool live = m != 0xFFFF;
+                // zero weights in front of the band: both loads are 128-bit
+                const float4* pp = reinterpret_cast<const float4*>(pbuf + (slot & 0xFFFF));
                 const float4* wg = reinterpret_cast<const float4*>(wts + a.goff[g]) + lane;
                 const int gm4 = a.gmax[g] >> 2;
                 // four independent partial sums (one per tap residue mod 4): fixed order, so deterministic,

@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B timing of two builds of the library (build_ab/libA.so, libB.so): 256-recording device-resident bench, twice each
-for rep in 1 2; do for v in A B; do
+for rep in 1 2; do for v in ${VARIANTS:-A B}; do
 cp build_ab/lib$v.so audio-analysis_b200/libcacophony_b200.so
 CAC_BENCH_RECORDINGS=256 CAC_BENCH_POOL=16 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e 2>/dev/null | python -c "
 import sys, json
