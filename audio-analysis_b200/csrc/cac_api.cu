@@ -235,7 +235,9 @@ extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_p
     // stream as soon as the samples they reference have arrived, and every finished chunk goes back to
     // the host on a third stream - upload, kernels and download overlap (full-duplex PCIe) when the
     // host buffers are page-locked; with pageable buffers the copies serialise but stay correct.
-    const int n_chunks = (int)std::min<int64_t>(16, (n + 73) / 74);
+    // chunks of ~156 segments: one wave of the persistent kernel (148 CTAs x ~23 stages) and ~50 MB per copy -
+    // small enough that the first download starts ~1.5 ms into the call, large enough for full PCIe rate
+    const int n_chunks = (int)std::min<int64_t>(256, std::max<int64_t>(1, (n + 77) / 156));
     const int64_t per_chunk = (n + n_chunks - 1) / n_chunks;
     const size_t work_chunk = (cac_features_work_bytes(plan, per_chunk) + 255) / 256 * 256;
     if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, work_chunk * n_chunks))) return rc;
