@@ -339,6 +339,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         cp_async_wait_all();
         __syncthreads();                       // raw has stage q; every warp is done with the previous stage
         if (q_prev >= 0) flush_tile(q_prev);   // (the barrier after the normalise pass orders this against new tile writes)
+        bool seg_nan = false;                  // constant segment: normalize_data divides 0 by 0 -> every value is NaN
         {   // raw -> normalised even/odd planes (normalize_data, exact float32 op order)
             const cac_segment sd = a.segs[seg];
             const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
@@ -349,6 +350,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             if (a.normalize) {
                 const float2 st = a.segstat[seg];
                 mn = st.x; range = __fsub_rn(st.y, st.x); rcp = __frcp_rn(range);
+                seg_nan = !(range > 0.f);
             }
             const bool fast_div = a.normalize && range > 1e-30f && range < 1e30f;
             const float4* raw4 = reinterpret_cast<const float4*>(raw);
@@ -425,6 +427,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             __syncwarp();
         }
         vmax = warp_max(vmax);
+        if (seg_nan) vmax = __uint_as_float(0x7fc00000u);     // fmaxf drops NaNs; np.max keeps them (bits order above every finite value)
         if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
         q_prev = q;
     }
@@ -462,15 +465,19 @@ __global__ void __launch_bounds__(256) seg_minmax_kernel(const float* __restrict
 // ---- librosa.power_to_db(S, ref=np.max), top_db = 80, per item ------------------------------
 // explicit _rn intrinsics: no FMA contraction, so the block maximum maps to exactly 0 dB as in numpy;
 // log_spec.max() is refdb - refdb = 0 when ref is the block maximum, so the floor is -top_db.
+// Comparisons instead of fmaxf so that NaN goes through as in np.maximum.
+__device__ __forceinline__ float db_ref(float vmax) {
+    return __fmul_rn(10.0f, log10f(vmax < 1e-10f ? 1e-10f : vmax));
+}
 __device__ __forceinline__ float db_value(float v, float refdb) {
-    const float d = __fsub_rn(__fmul_rn(10.0f, log10f(fmaxf(1e-10f, v))), refdb);
-    return fmaxf(d, -80.0f);
+    const float d = __fsub_rn(db_ref(v), refdb);
+    return d < -80.0f ? -80.0f : d;
 }
 // grid = (chunks per item, items): no per-element index arithmetic, 128-bit accesses when aligned
 __global__ void __launch_bounds__(256) power_to_db_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                           const unsigned* __restrict__ itemmax, long long item_len) {
     const long long item = blockIdx.y;
-    const float refdb = __fmul_rn(10.0f, log10f(fmaxf(1e-10f, __uint_as_float(itemmax[item]))));
+    const float refdb = db_ref(__uint_as_float(itemmax[item]));
     const float* src = in + item * item_len;
     float* dst = out + item * item_len;
     const long long stride = (long long)gridDim.x * 256;

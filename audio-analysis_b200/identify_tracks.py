@@ -86,6 +86,18 @@ def segment_descriptors(n_samples, sr, tracks, segment_length, stride, fmin=50, 
     return np.array(rows, dtype=SEGMENT_DTYPE).reshape(-1), counts
 
 
+class ParameterError(Exception):
+    """Stands in for librosa.util.exceptions.ParameterError (librosa itself is not a dependency of this package)."""
+
+
+def _check_finite(first_values):
+    """librosa.stft refuses non-finite audio (util.valid_audio).  The one way load_samples gets there is a
+    constant segment: normalize_data (src/identify_tracks.py:202-209) divides 0 by 0 and the whole segment is
+    NaN.  The kernels carry the NaNs through to the output like numpy would; the drop-in raises like librosa."""
+    if np.isnan(first_values).any():
+        raise ParameterError("Audio buffer is not finite everywhere")
+
+
 def _finish(block, mean_sub, channels):
     """get_spect tail (src/identify_tracks.py:267,282-287) on [n, n_mels, frames]."""
     block = block[..., None]
@@ -117,7 +129,9 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
         fmin, fmax, power, mel_break = 50, 11000, 2, None
     plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break,
                  int(sr * segment_length), int(power), bool(db_scale), bool(normalize))
-    block = _finish(plan.run_host(frames, segs), mean_sub, channels)
+    raw = plan.run_host(frames, segs)
+    _check_finite(raw[:, 0, 0])
+    block = _finish(raw, mean_sub, channels)
     out, k = [], 0
     for c in counts:
         out.append([block[k + i] for i in range(c)])
@@ -147,7 +161,9 @@ def load_samples_device(frames, sr, tracks, segment_length, stride, hop_length=2
     if len(segs) == 0:
         empty = torch.empty((0, int(n_mels), plan.n_frames, int(channels)), dtype=torch.float32, device=dev)
         return [empty for _ in counts]
-    block = engine.spect_tail(plan.run(frames, segs), mean_sub, channels)
+    raw = plan.run(frames, segs)
+    _check_finite(raw[:, 0, 0].cpu().numpy())
+    block = engine.spect_tail(raw, mean_sub, channels)
     out, k = [], 0
     for c in counts:
         out.append(block[k:k + c])

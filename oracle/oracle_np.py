@@ -23,11 +23,18 @@ def fft_frequencies(sr, n_fft):
     return np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
 
 
+class ParameterError(Exception):
+    """librosa.util.exceptions.ParameterError"""
+
+
 def stft(y, n_fft, hop_length):
     """librosa.stft defaults as called at src/identify_tracks.py:243,389,654 and
     src/identify_morepork.py:24: periodic Hann, win_length=n_fft, center=True with
-    zero padding, 1 + len(y)//hop frames, float64 rfft rounded to complex64."""
+    zero padding, 1 + len(y)//hop frames, float64 rfft rounded to complex64.  Like librosa it refuses
+    non-finite audio (util.valid_audio), which is what a constant segment becomes after normalize_data."""
     y = np.asarray(y, dtype=np.float32)
+    if not np.isfinite(y).all():
+        raise ParameterError("Audio buffer is not finite everywhere")
     win = scipy.signal.get_window("hann", n_fft, fftbins=True)
     ypad = np.pad(y, (n_fft // 2, n_fft // 2))
     n_frames = 1 + (len(ypad) - n_fft) // hop_length

@@ -24,6 +24,10 @@ def fft_frequencies(*, sr=22050, n_fft=2048):
     return np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
 
 
+class ParameterError(Exception):
+    """librosa.util.exceptions.ParameterError"""
+
+
 def stft(y, *, n_fft=2048, hop_length=None, win_length=None, window="hann",
          center=True, dtype=None, pad_mode="constant", out=None):
     """librosa.stft defaults: periodic Hann of win_length=n_fft, center=True with zero
@@ -36,6 +40,8 @@ def stft(y, *, n_fft=2048, hop_length=None, win_length=None, window="hann",
         win_length = n_fft
     assert win_length == n_fft and window == "hann" and center and pad_mode == "constant"
     y = np.asarray(y)
+    if not np.isfinite(y).all():                              # librosa.util.valid_audio
+        raise ParameterError("Audio buffer is not finite everywhere")
     if dtype is None:
         dtype = np.complex64 if y.dtype == np.float32 else np.complex128
     fft_window = scipy.signal.get_window("hann", win_length, fftbins=True)

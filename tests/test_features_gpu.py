@@ -207,3 +207,28 @@ def test_load_samples_device_tail_matches_host_path(engine):
     np.random.seed(5)
     got = T.load_samples_device(rec, 48000, [T.Signal(0.0, 9.0, 0, 24000)], mean_sub=True, channels=3, **kw)[0]
     assert np.abs(got.cpu().numpy() - np.stack(ref[0])).max() <= 1e-2
+
+
+def test_constant_segment_is_nan_like_numpy_and_raises_like_librosa(engine):
+    """Digital silence inside a track: normalize_data divides 0 by 0 (src/identify_tracks.py:202-209), numpy
+    carries NaN through stft / mel / power_to_db, librosa.stft raises ParameterError.  The C-ABI returns the NaNs
+    (only for the constant segments), the drop-in raises."""
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(77, seconds=9.0)
+    rec[3 * 48000:6 * 48000 + 10] = 0.25                      # segment k = 2 ([3 s, 6 s)) is constant
+    segs, counts = T.segment_descriptors(len(rec), 48000, [T.Signal(0.0, 9.0, 0, 24000)], 3.0, 1.5)
+    plan = T._plan(48000, 4096, 281, 160, 50, 11000, 1750, 144000, 2, True, True)
+    out = plan.run_host(rec, segs)
+    nan_seg = np.isnan(out).reshape(len(segs), -1)
+    assert nan_seg[2].all() and not nan_seg[[0, 1, 3, 4]].any()
+    power = T._plan(48000, 4096, 281, 160, 50, 11000, 1750, 144000, 2, False, True).run_host(rec, segs)
+    assert np.isnan(power[2]).all() and np.isfinite(power[[0, 1, 3, 4]]).all()
+    with pytest.raises(T.ParameterError):
+        T.load_samples(rec, 48000, [T.Signal(0.0, 9.0, 0, 24000)], 3.0, 1.5, db_scale=True, **S1)
+    with pytest.raises(O.ParameterError):
+        O.load_samples(rec, 48000, [O.Signal(0.0, 9.0, 0, 24000)], 3.0, 1.5, db_scale=True, **S1)
+    # without normalisation silence is legal: all-zero power -> 0 dB everywhere (max(1e-10, 0) on both sides)
+    quiet = np.zeros(144000, np.float32)
+    got = T.get_spect(quiet, 48000, 281, False, False, 1750, True, 160, 50, 11000, 4096, 2, True)
+    ref = O.get_spect(quiet, 48000, 281, False, False, 1750, True, 160, 50, 11000, 4096, 2, True)
+    assert np.array_equal(got, np.asarray(ref)) and float(np.abs(got).max()) == 0.0
