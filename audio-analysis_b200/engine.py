@@ -471,6 +471,34 @@ def spect_tail(block, mean_sub=False, channels=1):
     return out.view(n, n_mels, frames, channels)
 
 
+def bind_to_device_numa(device=0):
+    """Pin the calling process to the CPUs next to CUDA device `device` (NVML's ideal affinity) so that the
+    page-locked buffers it allocates afterwards live on that GPU's NUMA node.  One process per GPU that feeds
+    its GPU through *_host calls should call this first: without it two ranks can end up streaming through
+    the same socket's memory and the inter-socket link.  Returns the CPU list, or None when NVML cannot tell."""
+    torch = _torch()
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device).uuid)
+        if not uuid.startswith("GPU-"):
+            uuid = "GPU-" + uuid
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = [64 * w + b for w, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
 class pinned:
     """Context manager page-locking a numpy array for the duration of *_host calls (cac_host_register)."""
 

@@ -177,10 +177,23 @@ def main():
     from audio_analysis_b200 import engine, identify_tracks as T, sharding
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa_cpus = engine.bind_to_device_numa(local_rank)    # page-locked buffers below land next to this rank's GPU
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout when the communicator comes up; stdout is for the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
 
     # ---- inputs: a pool of unique synthetic recordings, replicated into distinct HBM buffers -----
     pool = make_pool(rank, POOL)                                   # [POOL, 2.88M] float32 host
@@ -314,7 +327,9 @@ def main():
                      "note": "FP32-pipe bound (75-110 flop/B, SURVEY.md 8d); HBM fraction reported as the metric asks"},
         "clocks": clocks, "checksum_first_recording": checksum,
     }
+    line["config"]["host_affinity"] = ("%d CPUs next to the GPU (NVML)" % len(numa_cpus)) if numa_cpus else "unchanged"
     if world == 1 and not args.no_cpu_baseline:
+        os.sched_setaffinity(0, all_cpus)                  # the CPU baseline may use every host core again
         cores = os.cpu_count() or 1
         n = max(cores, 8)
         v, wall = cpu_oracle_rate(n, cores)
