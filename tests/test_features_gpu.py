@@ -232,3 +232,37 @@ def test_constant_segment_is_nan_like_numpy_and_raises_like_librosa(engine):
     got = T.get_spect(quiet, 48000, 281, False, False, 1750, True, 160, 50, 11000, 4096, 2, True)
     ref = O.get_spect(quiet, 48000, 281, False, False, 1750, True, 160, 50, 11000, 4096, 2, True)
     assert np.array_equal(got, np.asarray(ref)) and float(np.abs(got).max()) == 0.0
+
+
+@pytest.mark.parametrize("hop,n_mels,brk,fmin,fmax,power,db,norm,seg_len,stride", [
+    (640, 160, 1000, 50, 11000, 2, True, True, 3.0, 1.5),      # classify's fallback hop / load_samples' default break
+    (281, 120, 1750, 50, 11000, 1, False, True, 3.0, 1.0),     # power 1, no dB, 4 row groups with dead slots
+    (281, 80, 1750, 100, 8000, 2, True, False, 2.5, 2.5),      # 3 row groups, no normalisation, other segment length
+    (512, 33, 1000, 500, 3000, 2, True, True, 1.0, 0.5),       # two groups with 31 dead slots, narrow band, short segments
+    (281, 200, 1750, 50, 11000, 2, False, True, 3.0, 1.5),     # 7 row groups (general gather path)
+])
+def test_parameter_sweep_vs_oracle(engine, hop, n_mels, brk, fmin, fmax, power, db, norm, seg_len, stride):
+    """Every parameter of load_samples is runtime data: other hops, filterbank sizes (exercising the
+    slot tables of mel_bands.h), band limits, power, dB and normalisation switches against the oracle."""
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(300 + hop + n_mels, seconds=7.0)
+    tracks = [(0.0, 7.0, 0, 24000), (0.4, 1.1, 700, 2500), (5.5, 7.0, 1000, 4000)]
+    kw = dict(hop_length=hop, mel_break=brk, n_mels=n_mels, fmin=fmin, fmax=fmax, power=power, db_scale=db,
+              normalize=norm, n_fft=4096)
+    np.random.seed(11)
+    got = T.load_samples(rec, 48000, [T.Signal(*t) for t in tracks], seg_len, stride, **kw)
+    np.random.seed(11)
+    ref = O.load_samples(rec, 48000, [O.Signal(*t) for t in tracks], seg_len, stride, **kw)
+    assert [len(g) for g in got] == [len(r) for r in ref]
+    n_cells = n_ok = 0
+    for g_track, r_track in zip(got, ref):
+        for g, r in zip(g_track, r_track):
+            r = np.asarray(r)
+            assert g.shape == r.shape
+            if db:
+                assert np.abs(g - r).max() <= 1e-2
+            else:
+                n_cells += r.size
+                n_ok += int(np.sum(np.abs(g - r) <= 1e-4 * np.abs(r) + 1e-30))
+    if not db:
+        assert n_ok >= 0.999 * n_cells
