@@ -20,8 +20,6 @@ constexpr int kNfft = 4096;
 constexpr int kExStride = 33;                 // floats per exchange row (odd -> conflict-free transpose)
 constexpr int kExFloats = 2 * 32 * kExStride; // one warp's exchange buffer: 32 rows x 33 float2
 constexpr int kWarpsPerCta = 12;               // 12 warps x 168 registers fill the register file
-constexpr int kTileFrames = 32;
-constexpr int kPStride = 33;                  // floats per power-spectrum row (bin): odd -> conflict-free both ways
 
 // ---- pass 1 input: 64 complex points z[32*i + lane] = (x[2n], x[2n+1]) * Hann ------------
 // Hann(s) = 0.5 - 0.5 cos(2 pi s / 4096) with s = 64*i + (2*lane + e): the cosine of the sum is
@@ -185,31 +183,18 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], pbuf, kmin, nbins);
 }
 
-// Correctly rounded x / d from a precomputed reciprocal (one Newton step on the residual): the
-// same result as __fdiv_rn for the normal-range operands normalize_data sees, at 3 FMA-pipe ops.
-__device__ __forceinline__ float div_by(float x, float d, float rcp) {
-    float q = x * rcp;
-    float r = fmaf(-q, d, x);
-    return fmaf(r, rcp, q);
-}
-
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
     int nbytes = valid ? 4 : 0;                    // 0 source bytes -> the 4 destination bytes are zero-filled
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
-}
-__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool valid) {
-    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    int nbytes = valid ? 16 : 0;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Shared-memory carve-up of stft_mel_kernel (floats unless noted); the launcher uses the same function.
 struct FeatSmem {
-    int raw;           // raw samples of the next stage as fetched by cp.async (stage_len + 8 floats)
-    int stage;         // 2 planes (even / odd samples) of stage_half floats: normalised samples of this stage
+    int raw;           // staging buffer of the odd stages: 2 planes (even / odd samples) of stage_half floats
+    int stage;         // staging buffer of the even stages, same shape
     int ex;            // 8 warps x kExFloats
     int wts;           // padded tap-major band weights (FeatArgs::wpad)
     int bands;         // int: slot table mstart[n_groups * 32] (mel_bands.h)
@@ -233,9 +218,9 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
 }
 
 // Persistent kernel, one CTA (8 warps) per SM.  Work unit = a "stage": frames_per_stage consecutive
-// frames of one segment.  The raw samples of stage q+G are fetched with cp.async (zero-filled
-// outside the real samples) into the second staging buffer while the warps transform stage q;
-// each warp owns whole frames: FFT -> power spectrum (own buffer) -> banded mel gather -> store.
+// frames of one segment.  The samples of stage q+1 are fetched with cp.async (zero-filled outside the
+// real samples) straight into the other pair of even / odd sample planes while the warps transform
+// stage q; each warp owns whole frames: FFT -> power spectrum (own buffer) -> banded mel gather -> tile.
 template <int POWER, int K2N>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const FeatArgs a) {
     extern __shared__ __align__(16) float smem[];
@@ -270,12 +255,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     const float* lt = ltab + lane;
 
     const long long n_stages = a.n_segs * a.stages_per_seg;
-    float* raw = smem + L.raw;
-    float* se = smem + L.stage;
-    float* so = se + a.stage_half;
-    // Stage q = frames [f0, f0+nfs) of one segment = staged elements u in [0, len), element u being real
-    // sample r0+u of the segment's PCM (zero outside [0, n_valid)).  raw[j] holds element u = j - shift with
-    // shift chosen so that raw[4i] is 16-byte aligned in global memory -> one 16-byte cp.async per 4 samples.
+    // two staging buffers, each a pair of planes (even / odd staged samples): stage q lives in buffer q & 1
+    auto plane_buf = [&](long long q) { return smem + ((q & 1) ? L.stage : L.raw); };
+    // Stage q = frames [f0, f0+nfs) of one segment = staged elements u in [0, len), element u being sample
+    // s = s0 + u of the zero-padded segment: the RAW sample (no normalisation, see below), zero in the np.pad
+    // region and outside the segment (librosa's centre padding).  4-byte cp.async straight into the planes:
+    // no alignment cases, no staging copy, no de-interleave pass.
     auto issue_stage = [&](long long q) {
         const long long seg = q / a.stages_per_seg;
         const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
@@ -283,23 +268,23 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         const int len = (nfs - 1) * a.hop + kNfft;
         const cac_segment sd = a.segs[seg];
         const float* src = a.pcm + sd.pcm_offset;
-        const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
-        const int shift = (int)(((sd.pcm_offset + r0) % 4 + 4) % 4);
-        const int n_chunks = (len + shift + 3) >> 2;
-        for (int i = tid; i < n_chunks; i += kWarpsPerCta * 32) {
-            const int r = r0 - shift + 4 * i;
-            if (r >= 0 && r + 3 < sd.n_valid) {
-                cp_async16(raw + 4 * i, src + r, true);
-            } else if (r + 3 < 0 || r >= sd.n_valid) {
-                cp_async16(raw + 4 * i, src, false);
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const bool valid = r + e >= 0 && r + e < sd.n_valid;
-                    cp_async4(raw + 4 * i + e, valid ? src + r + e : src, valid);
-                }
-            }
-        }
+        const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;      // index into the segment's real samples of u = 0
+        // thread t owns u = t, t + 384, ...: fixed plane (384 is even), plane index + 192 and source + 384 per step;
+        // [k_lo, k_hi) are its steps that meet a real sample, the others are zero-filled with plain stores
+        constexpr int kT = kWarpsPerCta * 32;
+        float* dst = plane_buf(q) + (tid & 1) * a.stage_half + (tid >> 1);
+        const int n_steps = (len - tid + kT - 1) / kT;                   // u = tid + kT k < len
+        const int first = r0 + tid;                                      // r of step 0
+        int k_lo = first >= 0 ? 0 : (-first + kT - 1) / kT;
+        int k_hi = sd.n_valid > first ? (sd.n_valid - first + kT - 1) / kT : 0;
+        k_lo = min(k_lo, n_steps);
+        k_hi = max(k_lo, min(k_hi, n_steps));
+        for (int k = 0; k < k_lo; ++k) dst[k * (kT / 2)] = 0.f;
+        const float* g = src + first + (long long)k_lo * kT;
+        float* d = dst + k_lo * (kT / 2);
+#pragma unroll 4
+        for (int k = k_lo; k < k_hi; ++k, g += kT, d += kT / 2) cp_async4(d, g, true);
+        for (int k = k_hi; k < n_steps; ++k) dst[k * (kT / 2)] = 0.f;
         cp_async_commit();
     };
 
@@ -325,6 +310,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         }
     };
 
+    // normalize_data is affine, x_n = alpha x + beta inside the segment (alpha = 2 / range,
+    // beta = 2 (1e-6 - 0.5 - min / range)), and the FFT is linear: for a frame that lies inside the segment
+    // FFT(w x_n) = alpha FFT(w x) + beta FFT(w), and the periodic Hann window's spectrum FFT(w) is zero
+    // from bin 2 on.  So the frames are transformed un-normalised and the mel values are scaled by alpha^2
+    // (power 2) or |alpha| (power 1).  Only stages that reach over a segment end (centre padding stays
+    // zero, so x_n = beta there would be wrong) - and every stage when a band touches bins 0 / 1 - get
+    // gamma = beta / alpha added to their in-segment samples first.
     // blocked distribution: every CTA owns a contiguous run of stages, so the samples two consecutive
     // stages (and the two 50 %-overlapping segments) share are re-read by the SAME CTA a moment later
     const long long q_begin = n_stages * blockIdx.x / gridDim.x, q_end = n_stages * (blockIdx.x + 1) / gridDim.x;
@@ -335,60 +327,40 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         const int len = (nfs - 1) * a.hop + kNfft;
+        float* se = plane_buf(q);
+        float* so = se + a.stage_half;
 
         cp_async_wait_all();
-        __syncthreads();                       // raw has stage q; every warp is done with the previous stage
-        if (q_prev >= 0) flush_tile(q_prev);   // (the barrier after the normalise pass orders this against new tile writes)
+        __syncthreads();                       // stage q has landed; every warp is done with stage q - 1
+        if (q + 1 < q_end) issue_stage(q + 1); // into the buffer stage q - 1 used
+        if (q_prev >= 0) flush_tile(q_prev);
+        float sc = 1.f;                        // output scale: alpha^2 / |alpha|
         bool seg_nan = false;                  // constant segment: normalize_data divides 0 by 0 -> every value is NaN
-        {   // raw -> normalised even/odd planes (normalize_data, exact float32 op order)
-            const cac_segment sd = a.segs[seg];
-            const int r0 = f0 * a.hop - kNfft / 2 - sd.pad_left;
-            const int shift = (int)(((sd.pcm_offset + r0) % 4 + 4) % 4);
-            const int n_chunks = (len + shift + 3) >> 2;
-            const int s0 = f0 * a.hop - kNfft / 2;            // segment sample index of staged element 0
-            float mn = 0.f, range = 1.f, rcp = 1.f;
-            if (a.normalize) {
-                const float2 st = a.segstat[seg];
-                mn = st.x; range = __fsub_rn(st.y, st.x); rcp = __frcp_rn(range);
-                seg_nan = !(range > 0.f);
-            }
-            const bool fast_div = a.normalize && range > 1e-30f && range < 1e30f;
-            const float4* raw4 = reinterpret_cast<const float4*>(raw);
-            // element e of chunk i is staged element u = 4i + e - shift; even u -> se[u/2], odd u -> so[u/2]
-            float* pa = (shift & 1) ? so : se;               // plane of elements e = 0, 2
-            float* pb = (shift & 1) ? se : so;               // plane of elements e = 1, 3
-            for (int i = tid; i < n_chunks; i += kWarpsPerCta * 32) {
-                const float4 v4 = raw4[i];
-                const int ub = 4 * i - shift;
-                const int sb = s0 + ub;
-                float v[4] = {v4.x, v4.y, v4.z, v4.w};
-                if (fast_div && ub >= 0 && ub + 3 < len && sb >= 0 && sb + 3 < a.seg_len) {
-                    // interior chunk: no bounds to honour, correctly rounded division via the reciprocal
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        float x = div_by(__fsub_rn(v[e], mn), range, rcp);
-                        v[e] = __fmul_rn(__fsub_rn(__fadd_rn(x, 0.000001f), 0.5f), 2.0f);
-                    }
-                    const int ia = ub >> 1, ib = (ub + 1) >> 1;
-                    pa[ia] = v[0]; pb[ib] = v[1]; pa[ia + 1] = v[2]; pb[ib + 1] = v[3];
-                } else {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int u = ub + e, sidx = sb + e;
-                        float x = v[e];
-                        if (a.normalize) {
-                            x = __fsub_rn(x, mn);
-                            x = fast_div ? div_by(x, range, rcp) : __fdiv_rn(x, range);
-                            x = __fmul_rn(__fsub_rn(__fadd_rn(x, 0.000001f), 0.5f), 2.0f);
-                        }
-                        if (sidx < 0 || sidx >= a.seg_len) x = 0.f;   // librosa's centre padding stays zero
-                        if (u >= 0 && u < len) ((u & 1) ? so : se)[u >> 1] = x;
+        if (a.normalize) {
+            const float2 st = a.segstat[seg];
+            const float range = __fsub_rn(st.y, st.x);
+            seg_nan = !(range > 0.f);
+            const float alpha = __fdividef(2.0f, range);
+            // ranges far from 1 (not audio in [-1, 1]): normalise the staged samples explicitly, scale stays 1
+            const bool explicit_norm = !(range > 1e-9f && range < 1e9f);
+            const int s0 = f0 * a.hop - kNfft / 2;                                  // segment index of u = 0
+            const bool edge = s0 < 0 || s0 + len > a.seg_len || a.kmin < 2;
+            if (!explicit_norm) sc = (POWER == 2) ? alpha * alpha : alpha;
+            if (edge || explicit_norm) {
+                const double gamma_d = (1e-6 - 0.5) * (double)range - (double)st.x;     // beta / alpha
+                const float mul = explicit_norm ? (float)(2.0 / (double)range) : 1.f;
+                const float add = explicit_norm ? (float)(2.0 / (double)range * gamma_d) : (float)gamma_d;
+                for (int u = tid; u < len; u += kWarpsPerCta * 32) {
+                    const int sidx = s0 + u;
+                    if (sidx >= 0 && sidx < a.seg_len) {
+                        float* e = se + (u & 1) * a.stage_half + (u >> 1);
+                        *e = fmaf(*e, mul, add);
                     }
                 }
             }
+            if (seg_nan) sc = __uint_as_float(0x7fc00000u);
         }
-        __syncthreads();                       // planes ready; raw is free again
-        if (q + 1 < q_end) issue_stage(q + 1);
+        __syncthreads();                       // the tile is flushed, the planes are final
 
         float vmax = 0.f;
 #pragma unroll 1
@@ -418,7 +390,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                     acc2 = fmaf(w.z, p.z, acc2);
                     acc3 = fmaf(w.w, p.w, acc3);
                 }
-                const float acc = (acc0 + acc1) + (acc2 + acc3);
+                const float acc = ((acc0 + acc1) + (acc2 + acc3)) * sc;
                 if (live) {
                     otile[m * tstride + fi] = acc;
                     vmax = fmaxf(vmax, acc);
@@ -445,8 +417,19 @@ __global__ void __launch_bounds__(256) seg_minmax_kernel(const float* __restrict
     const cac_segment sd = segs[seg];
     const float* p = pcm + sd.pcm_offset;
     float mn = INFINITY, mx = -INFINITY;
-    for (int i = threadIdx.x; i < sd.n_valid; i += 256) {
-        float v = __ldg(p + i);
+    // scalar head up to the first 16-byte boundary, 128-bit body (four loads in flight per thread), scalar tail
+    const int head = min(sd.n_valid, (int)((4 - ((reinterpret_cast<uintptr_t>(p) >> 2) & 3)) & 3));
+    const int n4 = (sd.n_valid - head) >> 2;
+    if ((int)threadIdx.x < head) { const float v = __ldg(p + threadIdx.x); mn = fminf(mn, v); mx = fmaxf(mx, v); }
+    const float4* p4 = reinterpret_cast<const float4*>(p + head);
+#pragma unroll 4
+    for (int i = threadIdx.x; i < n4; i += 256) {
+        const float4 v = __ldg(p4 + i);
+        mn = fminf(fminf(mn, v.x), fminf(v.y, fminf(v.z, v.w)));
+        mx = fmaxf(fmaxf(mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+    }
+    for (int i = head + 4 * n4 + threadIdx.x; i < sd.n_valid; i += 256) {
+        const float v = __ldg(p + i);
         mn = fminf(mn, v);
         mx = fmaxf(mx, v);
     }
