@@ -11,5 +11,5 @@ for f in *.cu; do
   $NVCC $FLAGS ${PTXAS_V:+-Xptxas -v} -c "$f" -o "${f%.cu}.o" &
 done
 wait
-$NVCC -shared -o "$OUT" *.o -lcudart
+$NVCC -shared -Wno-deprecated-gpu-targets -o "$OUT" *.o -lcudart
 echo "built $OUT"

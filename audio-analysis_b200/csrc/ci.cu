@@ -15,7 +15,6 @@
 
 namespace cac {
 
-constexpr int kCiN = 2048;
 constexpr int kCiWarps = 8;
 constexpr int kCiExStride = 33;                       // double2 per exchange row (odd: conflict-free transpose)
 constexpr int kCiExElems = 32 * kCiExStride;          // double2 per warp

@@ -16,7 +16,6 @@ namespace cac {
 
 constexpr int kWarps48 = 8;
 constexpr int kExStride48 = 33;                         // float2 per row of the Z matrix (odd: conflict-free)
-constexpr int kMaxRows48 = 75;
 
 // z[I] = (x[2n] w[2n], x[2n+1] w[2n+1]), n = lane + 32 I; w[s] = 0.5 - 0.5 cos(2 pi s / (64 R)), s = 64 I + (2 lane + e)
 template <int R, int I>
