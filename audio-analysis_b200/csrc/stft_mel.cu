@@ -66,10 +66,11 @@ struct Twid {
     float ar[4], ai[4];   // n2 = 0, 8, 16, 24
     float br[8], bi[8];   // n2 = 0..7
 };
-template <int N2>
-struct Pass2Tw {   // both halves per n2, so the A*B product is formed once and dies immediately
-    static __device__ __forceinline__ void run(float (&z0r)[32], float (&z0i)[32], float (&z1r)[32],
-                                               float (&z1i)[32], const Twid& tw) {
+// one half at a time (H = 0: z0, H = 1: z1 with the extra W64^(N2)): lets the first half's multiplies run
+// while the second half is still moving through shared memory, at the price of forming A*B twice
+template <int N2, int H>
+struct Pass2TwHalf {
+    static __device__ __forceinline__ void run(float (&zr)[32], float (&zi)[32], const Twid& tw) {
         if constexpr (N2 > 0) {
             constexpr int A = N2 >> 3, B = N2 & 7;
             float tr, ti;
@@ -79,15 +80,12 @@ struct Pass2Tw {   // both halves per n2, so the A*B product is formed once and 
                 tr = fmaf(-tw.ai[A], tw.bi[B], tw.ar[A] * tw.br[B]);
                 ti = fmaf(tw.ar[A], tw.bi[B], tw.ai[A] * tw.br[B]);
             }
-            float xr = z0r[N2], xi = z0i[N2];
-            z0r[N2] = fmaf(-xi, ti, xr * tr);
-            z0i[N2] = fmaf(xr, ti, xi * tr);
-            xr = z1r[N2]; xi = z1i[N2];
-            mul_twiddle<N2, 64>(xr, xi);
-            z1r[N2] = fmaf(-xi, ti, xr * tr);
-            z1i[N2] = fmaf(xr, ti, xi * tr);
+            float xr = zr[N2], xi = zi[N2];
+            if constexpr (H == 1) mul_twiddle<N2, 64>(xr, xi);
+            zr[N2] = fmaf(-xi, ti, xr * tr);
+            zi[N2] = fmaf(xr, ti, xi * tr);
         }
-        if constexpr (N2 + 1 < 32) Pass2Tw<N2 + 1>::run(z0r, z0i, z1r, z1i, tw);
+        if constexpr (N2 + 1 < 32) Pass2TwHalf<N2 + 1, H>::run(zr, zi, tw);
     }
 };
 
@@ -165,16 +163,14 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     ExWrite<0, 32>::run(ar, ai, ex2 + lane);
     __syncwarp();
     ExRead<0>::run(z1r, z1i, ex2 + lane * kExStride);
+    Twid tw;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { tw.ar[j] = lt[(8 + j) * 32]; tw.ai[j] = lt[(12 + j) * 32]; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { tw.br[j] = lt[(16 + j) * 32]; tw.bi[j] = lt[(24 + j) * 32]; }
+    Pass2TwHalf<0, 0>::run(z0r, z0i, tw);      // independent of the loads above: runs while they are in flight
     __syncwarp();   // pbuf aliases ex: nobody may still be reading the exchange rows when the power values land
-
-    {
-        Twid tw;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { tw.ar[j] = lt[(8 + j) * 32]; tw.ai[j] = lt[(12 + j) * 32]; }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { tw.br[j] = lt[(16 + j) * 32]; tw.bi[j] = lt[(24 + j) * 32]; }
-        Pass2Tw<0>::run(z0r, z0i, z1r, z1i, tw);
-    }
+    Pass2TwHalf<0, 1>::run(z1r, z1i, tw);
     fft_dif<32>(z0r, z0i);
     fft_dif<32>(z1r, z1i);
 
