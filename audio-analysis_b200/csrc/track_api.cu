@@ -8,10 +8,24 @@
 using namespace cac;
 
 namespace {
-struct Scratch {   // freed on every exit path
+struct Scratch {   // stream-ordered allocations (cached by the device's default memory pool), freed on every exit path
+    cudaStream_t st;
     void* p[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    ~Scratch() { for (void* q : p) if (q) cudaFree(q); }
+    explicit Scratch(cudaStream_t s) : st(s) {}
+    ~Scratch() { for (void* q : p) if (q) cudaFreeAsync(q, st); }
 };
+// keep freed scratch in the pool instead of returning it to the driver at every synchronisation
+void keep_pool_warm() {
+    static thread_local int done_for = -1;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev == done_for) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    done_for = dev;
+}
 }  // namespace
 
 extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
@@ -23,16 +37,17 @@ extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t 
         return fail(CAC_ERR_INVALID, "kernel size / max_components out of range");
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n = (size_t)rows * cols;
-    Scratch s;
+    keep_pool_warm();
+    Scratch s(st);
     float *d_t, *d_med;
     unsigned char *m0, *m1, *m2;
     int* d_small;
     // d_t doubles as the label array later (same size: 4 bytes per cell)
-    CUDA_TRY(cudaMalloc(&s.p[0], n * sizeof(float)));
-    CUDA_TRY(cudaMalloc(&s.p[1], n * sizeof(int)));
-    CUDA_TRY(cudaMalloc(&s.p[2], 3 * n));
-    CUDA_TRY(cudaMalloc(&s.p[3], ((size_t)rows + cols) * sizeof(float)));
-    CUDA_TRY(cudaMalloc(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int)));
+    CUDA_TRY(cudaMallocAsync(&s.p[0], n * sizeof(float), st));
+    CUDA_TRY(cudaMallocAsync(&s.p[1], n * sizeof(int), st));
+    CUDA_TRY(cudaMallocAsync(&s.p[2], 3 * n, st));
+    CUDA_TRY(cudaMallocAsync(&s.p[3], ((size_t)rows + cols) * sizeof(float), st));
+    CUDA_TRY(cudaMallocAsync(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int), st));
     d_t = (float*)s.p[0];
     int* d_rootid = (int*)s.p[1];
     m0 = (unsigned char*)s.p[2]; m1 = m0 + n; m2 = m1 + n;
