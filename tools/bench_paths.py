@@ -43,12 +43,21 @@ def bench_ci(hours=8.0):
     res = C.calculate_batch(pcm, [0], [n])[0]
     wall = time.perf_counter() - t0
     n_win = plan.window_count(n)
+    cpu = None
+    if os.environ.get("CAC_CPU_BASELINE", "1") != "0":       # the oracle port on a 10-minute slice, one process
+        from oracle import oracle_np as O
+        x = np.tile(pool[0], 10)
+        t0 = time.perf_counter()
+        O.calculate_from_array(x)
+        w = time.perf_counter() - t0
+        cpu = {"value": 600.0 / 3600.0 / w, "unit": "recording-hours/s", "cores": 1, "kind": "port",
+               "sample": "cacophony_index loop on a 10-minute 16 kHz slice, %.1f s wall" % w}
     algo = n * 4 + n_win * (80 + 1)
     print(json.dumps({"path": "cacophony_index (configs[3])", "recording_hours": hours, "samples": n, "windows": n_win,
                       "entries": len(res["cacophony_index_old"]), "ms_bins_plus_points": ms,
                       "recording_hours_per_s": hours / (ms * 1e-3), "algorithmic_GBps": algo / ms / 1e6,
                       "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "calculate_batch_wall_ms": wall * 1e3,
-                      "dtype": "f64"}), flush=True)
+                      "dtype": "f64", "cpu_baseline": cpu}), flush=True)
 
 
 def bench_morepork(n_rec=4096):
@@ -65,7 +74,16 @@ def bench_morepork(n_rec=4096):
         out = plan.run(pcm, out=out)[0]
     ms = timed(step, steps=5)
     algo = pcm.numel() * 4 + out.numel() * 4
-    print(json.dumps({"path": "identify_morepork (configs[2])", "recordings": n_rec, "ms": ms,
+    cpu = None
+    if os.environ.get("CAC_CPU_BASELINE", "1") != "0":       # the oracle port on 8 recordings, one process
+        from oracle import oracle_np as O
+        t0 = time.perf_counter()
+        for i in range(8):
+            O.morepork_windows(O.morepork_spectrogram(pool[i], 48000))
+        w = time.perf_counter() - t0
+        cpu = {"value": 8 * 60.0 / 3600.0 / w, "unit": "recording-hours/s", "cores": 1, "kind": "port",
+               "sample": "_load_sample STFT + window loop on 8 one-minute recordings, %.1f s wall" % w}
+    print(json.dumps({"path": "identify_morepork (configs[2])", "recordings": n_rec, "ms": ms, "cpu_baseline": cpu,
                       "recording_hours_per_s": n_rec / 60.0 / (ms * 1e-3), "algorithmic_GBps": algo / ms / 1e6,
                       "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "dtype": "f32"}), flush=True)
 
