@@ -46,6 +46,7 @@ struct cac_plan {
     std::string fused_unsupported;   // why cac_features_run cannot serve these parameters ("" = it can)
     // buffers owned by the *_host entry points
     float* d_pcm = nullptr;      size_t pcm_cap = 0;
+    short* d_pcm16 = nullptr;    size_t pcm16_cap = 0;   // staging of cac_features_host_pcm16
     cac_segment* d_segs = nullptr; size_t segs_cap = 0;
     float* d_out = nullptr;      size_t out_cap = 0;
     void* d_work = nullptr;      size_t work_cap = 0;
@@ -144,7 +145,7 @@ extern "C" int cac_plan_destroy(cac_plan* plan) {
     for (cudaEvent_t e : plan->ev_done) cudaEventDestroy(e);
     if (plan->s_h2d) { cudaStreamDestroy(plan->s_h2d); cudaStreamDestroy(plan->s_comp); cudaStreamDestroy(plan->s_d2h); }
     cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
-    cudaFree(plan->d_pcm); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
+    cudaFree(plan->d_pcm); cudaFree(plan->d_pcm16); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
     delete plan;
     return CAC_OK;
@@ -214,9 +215,21 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     return CAC_OK;
 }
 
-extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segs,
-                                 int64_t n, float* h_out) {
-    if (!plan || !h_pcm || !h_segs || !h_out) return fail(CAC_ERR_INVALID, "null argument");
+namespace cac {
+// 16-bit PCM -> float32 exactly as the decoders the reference uses do (sample / 32768)
+__global__ void __launch_bounds__(256) pcm16_to_float_kernel(const short* __restrict__ in, float* __restrict__ out,
+                                                             long long n) {
+    const long long stride = (long long)gridDim.x * 256;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += stride)
+        out[i] = (float)in[i] * (1.0f / 32768.0f);
+}
+}  // namespace cac
+
+static int features_host_impl(cac_plan* plan, const void* h_pcm_any, bool pcm16, int64_t n_pcm, const cac_segment* h_segs,
+                              int64_t n, float* h_out) {
+    const float* h_pcm = static_cast<const float*>(h_pcm_any);
+    const short* h_pcm16 = static_cast<const short*>(h_pcm_any);
+    if (!plan || !h_pcm_any || !h_segs || !h_out) return fail(CAC_ERR_INVALID, "null argument");
     if (n <= 0) return CAC_OK;
     CUDA_TRY(cudaSetDevice(plan->device));
     for (int64_t i = 0; i < n; ++i) {
@@ -229,6 +242,7 @@ extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_p
     const size_t out_bytes = (size_t)n * item * sizeof(float);
     int rc;
     if ((rc = ensure_cap(&plan->d_pcm, &plan->pcm_cap, (size_t)n_pcm * sizeof(float) + 16))) return rc;
+    if (pcm16 && (rc = ensure_cap(&plan->d_pcm16, &plan->pcm16_cap, (size_t)n_pcm * sizeof(short) + 16))) return rc;
     if ((rc = ensure_cap(&plan->d_segs, &plan->segs_cap, (size_t)n * sizeof(cac_segment)))) return rc;
     if ((rc = ensure_cap(&plan->d_out, &plan->out_cap, out_bytes))) return rc;
     // Pipeline: the PCM goes up in pieces on one stream, segment chunks are transformed on a second
@@ -262,8 +276,16 @@ extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_p
         for (int64_t i = s0; i < s1; ++i) need = std::max<int64_t>(need, h_segs[i].pcm_offset + h_segs[i].n_valid);
         need = std::min<int64_t>(n_pcm, (need + 3) / 4 * 4);
         if (need > sent) {
-            CUDA_TRY(cudaMemcpyAsync(plan->d_pcm + sent, h_pcm + sent, (size_t)(need - sent) * sizeof(float),
-                                     cudaMemcpyHostToDevice, plan->s_h2d));
+            if (pcm16) {       // half the bytes over PCIe, widened on the device right behind the copy
+                CUDA_TRY(cudaMemcpyAsync(plan->d_pcm16 + sent, h_pcm16 + sent, (size_t)(need - sent) * sizeof(short),
+                                         cudaMemcpyHostToDevice, plan->s_h2d));
+                const long long cnt = need - sent;
+                const unsigned blocks = (unsigned)std::min<long long>((cnt + 255) / 256, 148 * 8);
+                pcm16_to_float_kernel<<<blocks, 256, 0, plan->s_h2d>>>(plan->d_pcm16 + sent, plan->d_pcm + sent, cnt);
+            } else {
+                CUDA_TRY(cudaMemcpyAsync(plan->d_pcm + sent, h_pcm + sent, (size_t)(need - sent) * sizeof(float),
+                                         cudaMemcpyHostToDevice, plan->s_h2d));
+            }
             sent = need;
         }
         CUDA_TRY(cudaEventRecord(plan->ev_up[c], plan->s_h2d));
@@ -283,6 +305,16 @@ extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_p
     CUDA_TRY(cudaStreamSynchronize(plan->s_d2h));
     CUDA_TRY(cudaStreamSynchronize(plan->s_comp));
     return CAC_OK;
+}
+
+extern "C" int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segs,
+                                 int64_t n, float* h_out) {
+    return features_host_impl(plan, h_pcm, false, n_pcm, h_segs, n, h_out);
+}
+
+extern "C" int cac_features_host_pcm16(cac_plan* plan, const int16_t* h_pcm, int64_t n_pcm, const cac_segment* h_segs,
+                                       int64_t n, float* h_out) {
+    return features_host_impl(plan, h_pcm, true, n_pcm, h_segs, n, h_out);
 }
 
 extern "C" int cac_host_register(void* h_ptr, size_t bytes) {

@@ -46,6 +46,7 @@ lib.cac_features_work_bytes.argtypes = [_vp, _i64]
 lib.cac_features_work_bytes.restype = ctypes.c_size_t
 lib.cac_features_run.argtypes = [_vp, _vp, _vp, _i64, _vp, _vp, _vp]
 lib.cac_features_host.argtypes = [_vp, _vp, _i64, _vp, _i64, _vp]
+lib.cac_features_host_pcm16.argtypes = [_vp, _vp, _i64, _vp, _i64, _vp]
 lib.cac_normalize_run.argtypes = [_vp, _vp, _i64, _i32, _vp]
 lib.cac_mel_project_run.argtypes = [_vp, _vp, _i32, _vp, _vp]
 lib.cac_power_to_db_run.argtypes = [_vp, _vp, _i64, _i64, _vp, _vp]
@@ -90,7 +91,7 @@ lib.cac_resample_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
-           "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host",
+           "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
 
 
@@ -185,13 +186,16 @@ class FeaturePlan:
 
     # ---- host-buffer path (H2D + run + D2H inside the call) ----------------------------------
     def run_host(self, pcm, segments, out=None):
-        pcm = np.ascontiguousarray(pcm, dtype=np.float32).reshape(-1)
+        """Host arrays in, host array out.  int16 PCM (as decoded) is uploaded as is and widened on the device
+        to sample / 32768 (cac_features_host_pcm16); anything else is taken as float32."""
+        pcm16 = isinstance(pcm, np.ndarray) and pcm.dtype == np.int16
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16 if pcm16 else np.float32).reshape(-1)
         segments = np.ascontiguousarray(segments, dtype=SEGMENT_DTYPE)
         n = segments.shape[0]
         if out is None:
             out = np.empty((n, self.n_mels, self.n_frames), dtype=np.float32)
-        check(lib.cac_features_host(self._h, pcm.ctypes.data_as(_vp), pcm.size, segments.ctypes.data_as(_vp), n,
-                                    out.ctypes.data_as(_vp)))
+        fn = lib.cac_features_host_pcm16 if pcm16 else lib.cac_features_host
+        check(fn(self._h, pcm.ctypes.data_as(_vp), pcm.size, segments.ctypes.data_as(_vp), n, out.ctypes.data_as(_vp)))
         return out
 
     def mel_project(self, mag):

@@ -120,7 +120,8 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
                                   "(tf.image.resize_with_pad on a 2-D mfcc with *mel.shape); not built")
     if filter_freqs or filter_below:
         raise NotImplementedError("Butterworth pre-filter is a host pre-step outside this path")
-    frames = np.ascontiguousarray(frames, dtype=np.float32)
+    # int16 frames (PCM as decoded) are uploaded as they are and widened on the device to sample / 32768
+    frames = np.ascontiguousarray(frames, dtype=np.int16 if getattr(frames, "dtype", None) == np.int16 else np.float32)
     segs, counts = segment_descriptors(len(frames), sr, tracks, segment_length, stride, fmin, fmax,
                                        pad_short_tracks)
     if len(segs) == 0:

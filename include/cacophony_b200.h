@@ -88,6 +88,13 @@ int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_segment* d_se
  * cudaHostAlloc'ed / torch pin_memory buffer); returns after the last byte of h_out has landed. */
 int cac_features_host(cac_plan* plan, const float* h_pcm, int64_t n_pcm, const cac_segment* h_segments,
                       int64_t n_segments, float* h_out);
+
+/* Same call for 16-bit PCM as it leaves the decoder: samples are widened on the device to sample / 32768.0f,
+ * the value librosa.load / soundfile hand to identify_tracks.load_recording (src/identify_tracks.py:51-58) for
+ * 16-bit sources, so results equal cac_features_host on the widened array bit for bit; the upload is half
+ * the bytes, which matters because the host path runs at PCIe speed. */
+int cac_features_host_pcm16(cac_plan* plan, const int16_t* h_pcm, int64_t n_pcm, const cac_segment* h_segments,
+                            int64_t n_segments, float* h_out);
 /* Page-lock / release a caller-owned host buffer (cudaHostRegister) so that *_host calls can overlap copies. */
 int cac_host_register(void* h_ptr, size_t bytes);
 int cac_host_unregister(void* h_ptr);

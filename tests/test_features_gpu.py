@@ -266,3 +266,23 @@ def test_parameter_sweep_vs_oracle(engine, hop, n_mels, brk, fmin, fmax, power, 
                 n_ok += int(np.sum(np.abs(g - r) <= 1e-4 * np.abs(r) + 1e-30))
     if not db:
         assert n_ok >= 0.999 * n_cells
+
+
+def test_pcm16_host_path_equals_float_path(engine):
+    """16-bit PCM as decoded goes up as int16 (half the PCIe bytes) and is widened on the device to sample / 32768:
+    bit for bit the result of handing over the widened float32 array."""
+    from audio_analysis_b200 import identify_tracks as T
+    rec16 = np.round(synth.recording(5, seconds=7.5) * 32767.0).astype(np.int16)
+    recf = rec16.astype(np.float32) / np.float32(32768.0)
+    segs, _ = T.segment_descriptors(len(rec16), 48000, [T.Signal(0.0, 7.5, 0, 24000)], 3.0, 1.5)
+    plan = T._plan(48000, 4096, 281, 160, 50, 11000, 1750, 144000, 2, True, True)
+    a = plan.run_host(rec16, segs)
+    b = plan.run_host(recf, segs)
+    assert a.dtype == np.float32 and np.array_equal(a, b)
+    kw = dict(segment_length=3.0, stride=1.5, db_scale=True, **S1)
+    np.random.seed(3)
+    x = T.load_samples(rec16, 48000, [T.Signal(0.0, 7.5, 0, 24000), T.Signal(1.0, 2.0, 500, 5000)], **kw)
+    np.random.seed(3)
+    y = T.load_samples(recf, 48000, [T.Signal(0.0, 7.5, 0, 24000), T.Signal(1.0, 2.0, 500, 5000)], **kw)
+    assert [len(t) for t in x] == [len(t) for t in y]
+    assert all(np.array_equal(p, q) for s, t in zip(x, y) for p, q in zip(s, t))
