@@ -362,6 +362,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
 #pragma unroll 1
         for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
             fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt, a.kmin, a.nbins);
+#pragma unroll 1
             for (int i = a.nbins + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;   // zero-weight taps read zeros
             __syncwarp();
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
@@ -377,10 +378,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 // four independent partial sums (one per tap residue mod 4): fixed order, so deterministic,
                 // and the FMA chains of one group overlap instead of serialising on one accumulator
                 float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+                const float4* const pend = pp + gm4;
 #pragma unroll 2
-                for (int i = 0; i < gm4; ++i) {             // the padding taps add +0
-                    const float4 w = wg[i * 32];
-                    const float4 p = pp[i];
+                for (; pp != pend; ++pp, wg += 32) {        // the padding taps add +0
+                    const float4 w = *wg;
+                    const float4 p = *pp;
                     acc0 = fmaf(w.x, p.x, acc0);
                     acc1 = fmaf(w.y, p.y, acc1);
                     acc2 = fmaf(w.z, p.z, acc2);
