@@ -252,14 +252,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
 
     const long long n_stages = a.n_segs * a.stages_per_seg;
     // two staging buffers, each a pair of planes (even / odd staged samples): stage q lives in buffer q & 1
-    auto plane_buf = [&](long long q) { return smem + ((q & 1) ? L.stage : L.raw); };
+    auto plane_buf = [&](int parity) { return smem + (parity ? L.stage : L.raw); };
     // Stage q = frames [f0, f0+nfs) of one segment = staged elements u in [0, len), element u being sample
     // s = s0 + u of the zero-padded segment: the RAW sample (no normalisation, see below), zero in the np.pad
     // region and outside the segment (librosa's centre padding).  4-byte cp.async straight into the planes:
     // no alignment cases, no staging copy, no de-interleave pass.
-    auto issue_stage = [&](long long q) {
-        const long long seg = q / a.stages_per_seg;
-        const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
+    // stages are addressed as (segment, stage within the segment, buffer parity): no divisions in the loop
+    auto issue_stage = [&](int seg, int sidx, int parity) {
+        const int f0 = sidx * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         const int len = (nfs - 1) * a.hop + kNfft;
         const cac_segment sd = a.segs[seg];
@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         // thread t owns u = t, t + 384, ...: fixed plane (384 is even), plane index + 192 and source + 384 per step;
         // [k_lo, k_hi) are its steps that meet a real sample, the others are zero-filled with plain stores
         constexpr int kT = kWarpsPerCta * 32;
-        float* dst = plane_buf(q) + (tid & 1) * a.stage_half + (tid >> 1);
+        float* dst = plane_buf(parity) + (tid & 1) * a.stage_half + (tid >> 1);
         const int n_steps = (len - tid + kT - 1) / kT;                   // u = tid + kT k < len
         const int first = r0 + tid;                                      // r of step 0
         int k_lo = first >= 0 ? 0 : (-first + kT - 1) / kT;
@@ -287,9 +287,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     // The warps park a stage's mel values in otile ([mel][frame]); the whole CTA then writes every mel row's
     // frames_per_stage consecutive frames as one contiguous run (full 32-byte sectors instead of 4-byte
     // stores scattered over n_mels rows: no read-modify-write fills in L2 / HBM).
-    auto flush_tile = [&](long long qp) {
-        const long long seg = qp / a.stages_per_seg;
-        const int f0 = (int)(qp - seg * a.stages_per_seg) * a.frames_per_stage;
+    auto flush_tile = [&](int seg, int sidx) {
+        const int f0 = sidx * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         float* outseg = a.out + (size_t)seg * a.n_mels * a.n_frames + f0;
         constexpr int kThreads = kWarpsPerCta * 32;
@@ -297,7 +296,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             const int rows_per_iter = kThreads / nfs;
             int m = tid / nfs;
             const int f = tid - m * nfs;
-            for (; m < a.n_mels; m += rows_per_iter) outseg[(size_t)m * a.n_frames + f] = otile[m * tstride + f];
+            float* gp = outseg + (size_t)m * a.n_frames + f;
+            const float* sp = otile + m * tstride + f;
+            const size_t gstep = (size_t)rows_per_iter * a.n_frames;
+            const int sstep = rows_per_iter * tstride;
+            for (; m < a.n_mels; m += rows_per_iter, gp += gstep, sp += sstep) *gp = *sp;
         } else {
             for (int t = tid; t < a.n_mels * nfs; t += kThreads) {
                 const int m = t / nfs, f = t - m * nfs;
@@ -316,20 +319,22 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     // blocked distribution: every CTA owns a contiguous run of stages, so the samples two consecutive
     // stages (and the two 50 %-overlapping segments) share are re-read by the SAME CTA a moment later
     const long long q_begin = n_stages * blockIdx.x / gridDim.x, q_end = n_stages * (blockIdx.x + 1) / gridDim.x;
-    long long q = q_begin, q_prev = -1;
-    if (q < q_end) issue_stage(q);
-    for (; q < q_end; ++q) {
-        const long long seg = q / a.stages_per_seg;
-        const int f0 = (int)(q - seg * a.stages_per_seg) * a.frames_per_stage;
+    const int n_my = (int)(q_end - q_begin);
+    int seg = (int)(q_begin / a.stages_per_seg);
+    int sidx = (int)(q_begin - (long long)seg * a.stages_per_seg);
+    if (n_my > 0) issue_stage(seg, sidx, 0);
+    for (int it = 0; it < n_my; ++it) {
+        const int f0 = sidx * a.frames_per_stage;
         const int nfs = min(a.frames_per_stage, a.n_frames - f0);
         const int len = (nfs - 1) * a.hop + kNfft;
-        float* se = plane_buf(q);
+        float* se = plane_buf(it & 1);
         float* so = se + a.stage_half;
+        const bool last_of_seg = sidx + 1 == a.stages_per_seg;
 
         cp_async_wait_all();
         __syncthreads();                       // stage q has landed; every warp is done with stage q - 1
-        if (q + 1 < q_end) issue_stage(q + 1); // into the buffer stage q - 1 used
-        if (q_prev >= 0) flush_tile(q_prev);
+        if (it + 1 < n_my) issue_stage(last_of_seg ? seg + 1 : seg, last_of_seg ? 0 : sidx + 1, (it + 1) & 1);   // into the buffer stage q - 1 used
+        if (it > 0) flush_tile(sidx > 0 ? seg : seg - 1, sidx > 0 ? sidx - 1 : a.stages_per_seg - 1);
         float sc = 1.f;                        // output scale: alpha^2 / |alpha|
         bool seg_nan = false;                  // constant segment: normalize_data divides 0 by 0 -> every value is NaN
         if (a.normalize) {
@@ -399,10 +404,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         vmax = warp_max(vmax);
         if (seg_nan) vmax = __uint_as_float(0x7fc00000u);     // fmaxf drops NaNs; np.max keeps them (bits order above every finite value)
         if (lane == 0) atomicMax(a.segmax + seg, __float_as_uint(vmax));
-        q_prev = q;
+        if (last_of_seg) { ++seg; sidx = 0; } else ++sidx;
     }
     __syncthreads();
-    if (q_prev >= 0) flush_tile(q_prev);
+    if (n_my > 0) flush_tile(sidx > 0 ? seg : seg - 1, sidx > 0 ? sidx - 1 : a.stages_per_seg - 1);
 }
 
 // ---- per-segment min / max of the zero-padded segment (normalize_data's reductions) ---------
