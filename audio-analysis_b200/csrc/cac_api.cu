@@ -93,7 +93,7 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     plan->id = g_next_plan_id++;
     plan->n_frames = 1 + p.segment_samples / p.hop_length;
     const int bins = 1 + p.n_fft / 2;
-    const std::string berr = plan->mb.build(w, p.n_mels, bins);
+    const std::string berr = plan->mb.build(w, p.n_mels, bins, /*absolute=*/true);
     if (!berr.empty()) { delete plan; return fail(CAC_ERR_INVALID, berr); }
     const int kmin = plan->mb.kmin, kmax = plan->mb.kmax;
     if (p.n_fft != 4096) plan->fused_unsupported = "fused STFT->mel kernel supports n_fft == 4096 only";

@@ -16,11 +16,12 @@ struct MelBands {
     std::vector<float> weights;   // packed band weights (for the standalone projection kernel)
     int kmin = 0, kmax = 0;       // lowest / highest FFT bin any band touches
     std::vector<float> wpad;      // wpad[goff[g] + ((t/4)*32 + lane)*4 + t%4]
-    std::vector<int> mstart;      // [n_groups * 32] slot table: (first bin - kmin, rounded down to 4) | mel row << 16; row 0xFFFF = dead slot
+    std::vector<int> mstart;      // [n_groups * 32] slot table: (first bin - base bin, rounded down to 4) | mel row << 16; row 0xFFFF = dead slot
     int n_groups = 0, pbuf_len = 0, gmax[16] = {0}, goff[16] = {0};
 
     // returns "" or the reason the table cannot be built
-    std::string build(const float* w, int n_mels, int bins) {
+    // absolute = false: band starts (mstart) and pbuf_len are relative to bin kmin; true: relative to bin 0
+    std::string build(const float* w, int n_mels, int bins, bool absolute = false) {
         if (n_mels < 1 || n_mels > kMaxMels) return "n_mels out of range";
         int lo = bins, hi = -1;
         for (int m = 0; m < n_mels; ++m) {
@@ -39,6 +40,7 @@ struct MelBands {
             if (bt.len[m] == 0) bt.start[m] = (int16_t)lo;
         if ((int)weights.size() > kMaxTaps) return "filterbank has too many taps";
         kmin = lo;
+        const int kbase = absolute ? 0 : kmin;
         kmax = hi;
         n_groups = (n_mels + 31) / 32;
         // Row -> (group, lane) slots.  A 128-bit shared load serves 8 lanes per wavefront, so the 8 rows of a
@@ -48,7 +50,7 @@ struct MelBands {
         const int n_slots = n_groups * 32;
         std::vector<int> s0(n_mels), plen(n_mels), order(n_mels), slot_row(n_slots, -1);
         for (int m = 0; m < n_mels; ++m) {
-            s0[m] = bt.start[m] - kmin;
+            s0[m] = bt.start[m] - kbase;
             plen[m] = bt.len[m] + (s0[m] & 3);
             order[m] = m;
         }
@@ -73,7 +75,7 @@ struct MelBands {
             }
         }
         mstart.assign(n_slots, (int)0xFFFF0000u);            // dead slot: row 0xFFFF, start 0
-        int need = kmax - kmin + 1;
+        int need = kmax - kbase + 1;
         for (int g = 0; g < n_groups && g < 16; ++g) {
             int gm = 0;
             for (int l = 0; l < 32; ++l) {

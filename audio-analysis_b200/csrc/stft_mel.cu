@@ -96,8 +96,7 @@ template <int K2, int H, int K2N, int POWER>
 struct Untangle {
     static __device__ __forceinline__ void run(const float (&z0r)[32], const float (&z0i)[32],
                                                const float (&z1r)[32], const float (&z1i)[32], int lane,
-                                               int partner, float bc, float bs, float* pbuf, int kmin,
-                                               int nbins) {
+                                               int partner, float bc, float bs, float* pbuf_lane) {
         constexpr int pown = out_pos(32, K2);
         constexpr int psend = out_pos(32, 31 - K2);
         constexpr int psend0 = out_pos(32, (32 - K2) & 31);
@@ -123,10 +122,9 @@ struct Untangle {
         float xi = 0.5f * (sumi - tr);
         float p = fmaf(xr, xr, xi * xi);
         if constexpr (POWER == 1) p = sqrtf(p);
-        int kk = lane + 32 * H + 64 * K2 - kmin;
-        if (kk >= 0 && kk < nbins) pbuf[kk] = p;
+        pbuf_lane[32 * H + 64 * K2] = p;                   // pbuf is indexed by the absolute bin: no range checks
         if constexpr (K2 + 1 < K2N)
-            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, pbuf, kmin, nbins);
+            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, pbuf_lane);
     }
 };
 
@@ -136,11 +134,11 @@ struct LaneConsts {
 };
 
 // One warp: Hann-windowed 4096-point real FFT of the frame starting at staged sample u0,
-// power spectrum of bins [kmin, kmin+nbins) written to the warp's own buffer pbuf[bin - kmin].
+// power spectrum of bins [0, 64 K2N) written to the warp's own buffer pbuf[bin].
 template <int POWER, int K2N>
 __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const float* __restrict__ so, int u0,
                                           float* __restrict__ ex, float* __restrict__ pbuf, int lane,
-                                          const float* __restrict__ lt, int kmin, int nbins) {
+                                          const float* __restrict__ lt) {
     // lt: per-lane constants parked in shared memory ([28][32], see stft_mel_kernel) and re-read per
     // frame so they do not occupy registers next to the 128 data registers of the FFT
     float ar[64], ai[64];
@@ -175,8 +173,8 @@ __device__ __forceinline__ void fft_frame(const float* __restrict__ se, const fl
     fft_dif<32>(z1r, z1i);
 
     const int partner = (32 - lane) & 31;
-    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], pbuf, kmin, nbins);
-    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], pbuf, kmin, nbins);
+    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], pbuf + lane);
+    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], pbuf + lane);
 }
 
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
@@ -366,9 +364,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         float vmax = 0.f;
 #pragma unroll 1
         for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
-            fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt, a.kmin, a.nbins);
+            fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt);
 #pragma unroll 1
-            for (int i = a.nbins + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;   // zero-weight taps read zeros
+            for (int i = 64 * K2N + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;  // zero-weight taps past the computed bins read zeros
             __syncwarp();
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
 #pragma unroll 1
