@@ -122,10 +122,23 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     if (plan->fused_unsupported.empty()) {
         cudaSetDevice(device);
         cudaError_t e1 = cudaMalloc((void**)&plan->d_wpad, plan->mb.wpad.size() * sizeof(float) + 16);
-        cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, plan->mb.mstart.size() * sizeof(int) + 16);
+        // slot table of the fused kernel, one int4 per (group, lane): x = first bin of the band (multiple of 4),
+        // y = offset of the mel row in the output tile (-1: dead slot), z = offset of the lane's first weight quad,
+        // w = quads per row of this group - everything a lane needs for one group in a single 128-bit load
+        std::vector<int> slots(plan->mb.mstart.size() * 4);
+        for (size_t i = 0; i < plan->mb.mstart.size(); ++i) {
+            const int g = (int)(i / 32), lane = (int)(i % 32);
+            const unsigned packed = (unsigned)plan->mb.mstart[i];
+            const int row = (int)(packed >> 16);
+            slots[4 * i + 0] = (int)(packed & 0xFFFFu);
+            slots[4 * i + 1] = row == 0xFFFF ? -1 : row * (plan->frames_per_stage + 1);
+            slots[4 * i + 2] = (g < 16 ? plan->mb.goff[g] : 0) + lane * 4;
+            slots[4 * i + 3] = (g < 16 ? plan->mb.gmax[g] : 0) >> 2;
+        }
+        cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, slots.size() * sizeof(int) + 16);
         if (e1 == cudaSuccess && e2 == cudaSuccess) {
             e1 = cudaMemcpy(plan->d_wpad, plan->mb.wpad.data(), plan->mb.wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
-            e2 = cudaMemcpy(plan->d_mstart, plan->mb.mstart.data(), plan->mb.mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
+            e2 = cudaMemcpy(plan->d_mstart, slots.data(), slots.size() * sizeof(int), cudaMemcpyHostToDevice);
         }
         if (e1 != cudaSuccess || e2 != cudaSuccess) {
             cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);

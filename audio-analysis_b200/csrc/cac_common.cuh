@@ -38,7 +38,7 @@ struct FeatArgs {
     // longest band (multiple of 4); stored as float4 per (tap quad, lane):
     // wpad[goff[g] + ((t/4)*32 + lane)*4 + t%4] -> conflict-free 128-bit reads without predicates.
     const float* wpad;
-    const int* mstart;     // [n_groups * 32] slot table (mel_bands.h): band start (multiple of 4) | mel row << 16
+    const int* mstart;     // [n_groups * 32] int4 slot table (cac_api.cu): band start, tile offset of the row (-1 dead), weight offset, quads
     int n_groups;
     int pbuf_len;          // floats per warp power-spectrum buffer (covers the padded reads)
     int gmax[16];          // padded band length of group g

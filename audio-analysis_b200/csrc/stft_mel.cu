@@ -191,7 +191,7 @@ struct FeatSmem {
     int stage;         // staging buffer of the even stages, same shape
     int ex;            // 8 warps x kExFloats
     int wts;           // padded tap-major band weights (FeatArgs::wpad)
-    int bands;         // int: slot table mstart[n_groups * 32] (mel_bands.h)
+    int bands;         // int4 slot table [n_groups * 32] (cac_api.cu)
     int ltab;          // 32 x 32
     int otile;         // n_mels x (frames_per_stage + 1): this stage's mel values, flushed as row segments
     int total;
@@ -203,7 +203,7 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
     L.stage = o; o += 2 * stage_half;
     L.ex = o; o += kWarpsPerCta * kExFloats;
     L.wts = o; o += (n_taps + 3) / 4 * 4;
-    L.bands = o; o += (n_mels + 31) / 32 * 32;
+    L.bands = o; o += (n_mels + 31) / 32 * 32 * 4;
     o = (o + 31) / 32 * 32;
     L.ltab = o; o += 32 * 32;
     L.otile = o; o += n_mels * (frames_per_stage + 1);
@@ -223,14 +223,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     float* ex = smem + L.ex + warp * kExFloats;
     float* pbuf = ex;   // the power spectrum reuses the warp's exchange buffer once pass 2 has read it
     float* wts = smem + L.wts;
-    int* mstart = reinterpret_cast<int*>(smem + L.bands);
+    int4* slots = reinterpret_cast<int4*>(smem + L.bands);
     float* ltab = smem + L.ltab;
     float* otile = smem + L.otile;
     const int tstride = a.frames_per_stage + 1;       // odd row stride: conflict-free both ways
 
     // ---- one-time tables ------------------------------------------------------------------------
     for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
-    for (int m = tid; m < a.n_groups * 32; m += kWarpsPerCta * 32) mstart[m] = a.mstart[m];
+    for (int m = tid; m < a.n_groups * 32; m += kWarpsPerCta * 32) slots[m] = reinterpret_cast<const int4*>(a.mstart)[m];
     if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
         float s, c;
         sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
@@ -371,13 +371,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             // banded mel projection of this frame: lane owns mel rows lane, lane+32, ...
 #pragma unroll 1
             for (int g = 0; g < a.n_groups; ++g) {
-                const int slot = mstart[g * 32 + lane];      // (band start rounded down to 4 bins) | row << 16
-                const int m = (int)((unsigned)slot >> 16);
-                const bool live = m != 0xFFFF;
+                const int4 slot = slots[g * 32 + lane];      // band start | tile offset of the row | weight offset | quads
                 // zero weights in front of the band: both loads are 128-bit
-                const float4* pp = reinterpret_cast<const float4*>(pbuf + (slot & 0xFFFF));
-                const float4* wg = reinterpret_cast<const float4*>(wts + a.goff[g]) + lane;
-                const int gm4 = a.gmax[g] >> 2;
+                const float4* pp = reinterpret_cast<const float4*>(pbuf + slot.x);
+                const float4* wg = reinterpret_cast<const float4*>(wts + slot.z);
+                const int gm4 = slot.w;
                 // four independent partial sums (one per tap residue mod 4): fixed order, so deterministic,
                 // and the FMA chains of one group overlap instead of serialising on one accumulator
                 float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
@@ -392,8 +390,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                     acc3 = fmaf(w.w, p.w, acc3);
                 }
                 const float acc = ((acc0 + acc1) + (acc2 + acc3)) * sc;
-                if (live) {
-                    otile[m * tstride + fi] = acc;
+                if (slot.y >= 0) {
+                    otile[slot.y + fi] = acc;
                     vmax = fmaxf(vmax, acc);
                 }
             }
