@@ -137,7 +137,11 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
         }
         cudaError_t e2 = cudaMalloc((void**)&plan->d_mstart, slots.size() * sizeof(int) + 16);
         if (e1 == cudaSuccess && e2 == cudaSuccess) {
-            e1 = cudaMemcpy(plan->d_wpad, plan->mb.wpad.data(), plan->mb.wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
+            // the fused kernel leaves out the untangle's factor 1/2 (power 2: 1/4): exact powers of two, folded in here
+            std::vector<float> wscaled(plan->mb.wpad);
+            const float fold = p.power == 2 ? 0.25f : 0.5f;
+            for (float& v : wscaled) v *= fold;
+            e1 = cudaMemcpy(plan->d_wpad, wscaled.data(), wscaled.size() * sizeof(float), cudaMemcpyHostToDevice);
             e2 = cudaMemcpy(plan->d_mstart, slots.data(), slots.size() * sizeof(int), cudaMemcpyHostToDevice);
         }
         if (e1 != cudaSuccess || e2 != cudaSuccess) {

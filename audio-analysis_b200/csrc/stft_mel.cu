@@ -118,8 +118,9 @@ struct Untangle {
         mul_twiddle<K2, 64>(dr, di);                         // W4096^(64*K2)
         float tr = fmaf(di, bs, dr * bc);                    // * W4096^(lane + 32H) = (bc, -bs)
         float ti = fmaf(-dr, bs, di * bc);
-        float xr = 0.5f * (sumr + ti);
-        float xi = 0.5f * (sumi - tr);
+        // 2 X[k]: the factor 1/2 of the untangle (1/4 of the power) is folded into the mel weights on the host
+        float xr = sumr + ti;
+        float xi = sumi - tr;
         float p = fmaf(xr, xr, xi * xi);
         if constexpr (POWER == 1) p = sqrtf(p);
         pbuf_lane[32 * H + 64 * K2] = p;                   // pbuf is indexed by the absolute bin: no range checks
