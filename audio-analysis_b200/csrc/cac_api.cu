@@ -11,8 +11,11 @@
 #include "api_util.h"
 #include "cac_common.cuh"
 #include "mel_bands.h"
+#include "spec.cuh"
 
 namespace cac {
+cudaError_t launch_segment_rows(const float* pcm, const cac_segment* segs, long long n, float* rows, int seg_len,
+                                int n_frames, int normalize, long long* tab, cudaStream_t st);
 cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st);
 size_t feat_smem_bytes(const FeatArgs& a);
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
@@ -43,7 +46,15 @@ struct cac_plan {
     int frames_per_stage, stage_half;
     float* d_wpad = nullptr;
     int* d_mstart = nullptr;
-    std::string fused_unsupported;   // why cac_features_run cannot serve these parameters ("" = it can)
+    std::string fused_unsupported;   // why the fused kernel cannot serve these parameters ("" = it can)
+    // general path (fused_unsupported set, n_fft one of the framed-spectrum kernel's lengths): segment rows ->
+    // spec4800_kernel with mel epilogue -> power_to_db
+    bool general = false;
+    MelBands gmb;                    // band table relative to the lowest bin (stft4800.cu convention)
+    float2* d_ltab = nullptr;
+    float2* d_rtab = nullptr;
+    float* d_gwpad = nullptr;
+    int* d_gmstart = nullptr;
     // buffers owned by the *_host entry points
     float* d_pcm = nullptr;      size_t pcm_cap = 0;
     short* d_pcm16 = nullptr;    size_t pcm16_cap = 0;   // staging of cac_features_host_pcm16
@@ -119,6 +130,35 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     }
     if (!plan->frames_per_stage && plan->fused_unsupported.empty())
         plan->fused_unsupported = "parameters exceed the shared-memory budget of the fused kernel";
+    if (!plan->fused_unsupported.empty() && spec4800_supported(p.n_fft)) {
+        const std::string gerr = plan->gmb.build(w, p.n_mels, bins);
+        SpecArgs probe{};
+        probe.n_fft = p.n_fft;
+        probe.n_mels = p.n_mels;
+        probe.n_taps = (int)plan->gmb.wpad.size();
+        probe.pbuf_len = plan->gmb.pbuf_len;
+        if (gerr.empty() && plan->gmb.n_groups <= 16 && spec4800_smem_bytes(probe) <= 227 * 1024) {
+            cudaSetDevice(device);
+            std::vector<float2> lt(kSpec4800LtabRows * 32), rt(kSpec4800Rounds);
+            spec4800_host_tables(p.n_fft, plan->gmb.kmin, lt.data(), rt.data());
+            cudaError_t e = cudaMalloc((void**)&plan->d_ltab, lt.size() * sizeof(float2));
+            if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_rtab, rt.size() * sizeof(float2));
+            if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_gwpad, plan->gmb.wpad.size() * sizeof(float) + 16);
+            if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_gmstart, plan->gmb.mstart.size() * sizeof(int) + 16);
+            if (e == cudaSuccess) e = cudaMemcpy(plan->d_ltab, lt.data(), lt.size() * sizeof(float2), cudaMemcpyHostToDevice);
+            if (e == cudaSuccess) e = cudaMemcpy(plan->d_rtab, rt.data(), rt.size() * sizeof(float2), cudaMemcpyHostToDevice);
+            if (e == cudaSuccess)
+                e = cudaMemcpy(plan->d_gwpad, plan->gmb.wpad.data(), plan->gmb.wpad.size() * sizeof(float), cudaMemcpyHostToDevice);
+            if (e == cudaSuccess)
+                e = cudaMemcpy(plan->d_gmstart, plan->gmb.mstart.data(), plan->gmb.mstart.size() * sizeof(int), cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) {
+                cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_gwpad); cudaFree(plan->d_gmstart);
+                delete plan;
+                return fail(CAC_ERR_ALLOC, "could not upload the spectrum tables");
+            }
+            plan->general = true;
+        }
+    }
     if (plan->fused_unsupported.empty()) {
         cudaSetDevice(device);
         cudaError_t e1 = cudaMalloc((void**)&plan->d_wpad, plan->mb.wpad.size() * sizeof(float) + 16);
@@ -162,6 +202,7 @@ extern "C" int cac_plan_destroy(cac_plan* plan) {
     for (cudaEvent_t e : plan->ev_done) cudaEventDestroy(e);
     if (plan->s_h2d) { cudaStreamDestroy(plan->s_h2d); cudaStreamDestroy(plan->s_comp); cudaStreamDestroy(plan->s_d2h); }
     cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
+    cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_gwpad); cudaFree(plan->d_gmstart);
     cudaFree(plan->d_pcm); cudaFree(plan->d_pcm16); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
     if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
     delete plan;
@@ -191,20 +232,68 @@ extern "C" int cac_plan_last_kernel_ms(cac_plan* plan, float* ms) {
 
 extern "C" int cac_plan_frames(const cac_plan* plan) { return plan ? plan->n_frames : CAC_ERR_INVALID; }
 
+static size_t align128(size_t v) { return (v + 127) / 128 * 128; }
+
 extern "C" size_t cac_features_work_bytes(const cac_plan* plan, int64_t n) {
-    (void)plan;
-    return (size_t)(n > 0 ? n : 0) * (sizeof(float2) + sizeof(unsigned)) + 256;
+    const size_t nn = (size_t)(n > 0 ? n : 0);
+    size_t bytes = nn * (sizeof(float2) + sizeof(unsigned)) + 256;
+    if (plan && plan->general)   // item tables + the zero-padded, normalised segments as rows
+        bytes = align128(bytes) + align128((3 * nn + 1) * sizeof(long long)) +
+                nn * (size_t)plan->p.segment_samples * sizeof(float) + 128;
+    return bytes;
+}
+
+// general path of cac_features_run (see cac_plan::general)
+static int features_run_general(cac_plan* plan, const float* d_pcm, const cac_segment* d_segs, int64_t n, float* d_out,
+                                void* d_work, cudaStream_t st) {
+    const size_t nn = (size_t)n;
+    unsigned* segmax = (unsigned*)((char*)d_work + ((nn * sizeof(float2) + 127) / 128) * 128);   // same slot as the fused path
+    char* base = (char*)d_work + align128(nn * (sizeof(float2) + sizeof(unsigned)) + 256);
+    long long* tab = (long long*)base;
+    float* rows = (float*)(base + align128((3 * nn + 1) * sizeof(long long)));
+    CUDA_TRY(launch_segment_rows(d_pcm, d_segs, n, rows, plan->p.segment_samples, plan->n_frames, plan->p.normalize, tab, st));
+    SpecArgs a{};
+    a.pcm = rows;
+    a.item_off = tab;
+    a.item_len = tab + n;
+    a.frame_base = tab + 2 * n;
+    a.n_items = (int)n;
+    a.n_frames_total = (long long)n * plan->n_frames;
+    a.n_fft = plan->p.n_fft;
+    a.hop = plan->p.hop_length;
+    a.power = plan->p.power;
+    a.kmin = plan->gmb.kmin;
+    a.nbins = plan->gmb.kmax - plan->gmb.kmin + 1;
+    a.n_mels = plan->p.n_mels;
+    a.bin_major = 0;
+    a.out = d_out;
+    a.gmax = nullptr;
+    a.ltab = plan->d_ltab;
+    a.rtab = plan->d_rtab;
+    a.wpad = plan->d_gwpad;
+    a.mstart = plan->d_gmstart;
+    a.n_taps = (int)plan->gmb.wpad.size();
+    a.n_groups = plan->gmb.n_groups;
+    a.pbuf_len = plan->gmb.pbuf_len;
+    for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->gmb.gmax[g]; a.goff[g] = plan->gmb.goff[g]; }
+    CUDA_TRY(launch_spec4800(a, st));
+    if (plan->p.db_scale)
+        CUDA_TRY(launch_power_to_db(d_out, d_out, n, (long long)plan->p.n_mels * plan->n_frames, segmax, st));
+    return CAC_OK;
 }
 
 extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_segment* d_segs, int64_t n,
                                 float* d_out, void* d_work, void* stream) {
     if (!plan || !d_pcm || !d_segs || !d_out || !d_work) return fail(CAC_ERR_INVALID, "null argument");
-    if (!plan->fused_unsupported.empty()) return fail(CAC_ERR_INVALID, plan->fused_unsupported);
+    if (!plan->fused_unsupported.empty() && !plan->general)
+        return fail(CAC_ERR_INVALID, plan->fused_unsupported + "; the general path needs n_fft 4800 / 3200 / 1600 / "
+                                                               "4096 / 2048 / 1024 / 512");
     if (n == 0) return CAC_OK;
     if (((uintptr_t)d_pcm & 15) != 0) return fail(CAC_ERR_INVALID, "d_pcm must be 16-byte aligned");
     if (n < 0 || n > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "n_segments out of range");
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(plan->device));
+    if (plan->general) return features_run_general(plan, d_pcm, d_segs, n, d_out, d_work, st);
     int rc = ensure_constants(plan, st);
     if (rc) return rc;
     FeatArgs a{};

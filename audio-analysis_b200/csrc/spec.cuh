@@ -13,7 +13,7 @@ struct SpecArgs {
     const long long* frame_base;   // [n_items + 1] prefix sum of frames
     int n_items;
     long long n_frames_total;
-    int n_fft;                     // 4800 or 1600
+    int n_fft;                     // see spec4800_supported()
     int hop;
     int power;                     // 1: |X|, 2: |X|^2
     // output selection
@@ -32,6 +32,7 @@ struct SpecArgs {
     int gmax_taps[16], goff[16];
 };
 
+bool spec4800_supported(int n_fft);   // frame lengths the kernel is instantiated for (64 R points)
 size_t spec4800_smem_bytes(const SpecArgs& a);
 cudaError_t launch_spec4800(const SpecArgs& a, cudaStream_t st);
 // host-built tables for the 4800-point kernel: ltab [21][32] float2, rtab [76] float2

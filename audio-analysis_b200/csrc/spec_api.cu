@@ -21,15 +21,32 @@ struct cac_spec_plan {
     int* d_mstart = nullptr;
     long long* d_tab = nullptr;   size_t tab_cap = 0;    // item tables staged per call
     long long* d_wtab = nullptr;  size_t wtab_cap = 0;   // morepork window tables
+    bool dft = false;             // any other frame length: direct band DFT (band_dft.cu), raw bands only
+    float2* d_tw = nullptr;
 };
+
+namespace cac {
+void band_dft_host_table(int n_fft, float2* tw);
+size_t band_dft_smem_bytes(int n_fft);
+cudaError_t launch_band_dft(const SpecArgs& a, const float2* tw, cudaStream_t st);
+}  // namespace cac
+
+// librosa.stft(center=True): 1 + (n + 2 (n_fft // 2) - n_fft) // hop frames (= 1 + n // hop for even n_fft)
+static long long frames_of(const cac_spec_plan* plan, long long n) {
+    const long long padded = n + 2LL * (plan->p.n_fft / 2);
+    return padded >= plan->p.n_fft ? 1 + (padded - plan->p.n_fft) / plan->p.hop_length : 0;
+}
 
 extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* h_mel_weights, int device,
                                     cac_spec_plan** out) {
     if (!params || !out) return fail(CAC_ERR_INVALID, "null argument");
     const cac_spec_params& p = *params;
-    if (p.n_fft != 4800 && p.n_fft != 1600 && p.n_fft != 4096)
+    const bool dft = !spec4800_supported(p.n_fft);
+    if (dft && (p.n_mels != 0 || p.n_fft < 2 || band_dft_smem_bytes(p.n_fft) > 227 * 1024 || p.bin_hi - p.bin_lo > 512))
         return fail(CAC_ERR_INVALID,
-                    "framed-spectrum kernels are built for n_fft 4800 / 1600 (sr // 10 at 48 / 16 kHz) and 4096");
+                    "framed-spectrum kernels are built for n_fft 4800 / 3200 / 1600 (sr // 10 at 48 / 32 / 16 kHz), "
+                    "4096, 2048, 1024 and 512; any other n_fft up to 19,000 is served for raw bands of at most 512 "
+                    "bins only (direct band DFT)");
     if (p.hop_length < 1 || p.hop_length > p.n_fft) return fail(CAC_ERR_INVALID, "hop_length out of range");
     if (p.power != 1 && p.power != 2) return fail(CAC_ERR_INVALID, "power must be 1 or 2");
     if (p.n_mels < 0 || p.n_mels > kMaxMels) return fail(CAC_ERR_INVALID, "n_mels out of range");
@@ -55,6 +72,20 @@ extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* 
     } else {
         plan->kmin = p.bin_lo;
         plan->nbins = p.bin_hi - p.bin_lo;
+    }
+    if (dft) {
+        plan->dft = true;
+        std::vector<float2> tw(p.n_fft);
+        band_dft_host_table(p.n_fft, tw.data());
+        cudaError_t e = cudaMalloc((void**)&plan->d_tw, tw.size() * sizeof(float2));
+        if (e == cudaSuccess) e = cudaMemcpy(plan->d_tw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            cudaFree(plan->d_tw);
+            delete plan;
+            return fail(CAC_ERR_ALLOC, std::string("could not upload the DFT table: ") + cudaGetErrorString(e));
+        }
+        *out = plan;
+        return CAC_OK;
     }
     SpecArgs probe{};
     probe.n_fft = p.n_fft;
@@ -92,14 +123,14 @@ extern "C" int cac_spec_plan_destroy(cac_spec_plan* plan) {
     if (!plan) return CAC_OK;
     cudaSetDevice(plan->device);
     cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
-    cudaFree(plan->d_tab); cudaFree(plan->d_wtab);
+    cudaFree(plan->d_tab); cudaFree(plan->d_wtab); cudaFree(plan->d_tw);
     delete plan;
     return CAC_OK;
 }
 
 extern "C" int64_t cac_spec_frame_count(const cac_spec_plan* plan, int64_t n_samples) {
     if (!plan || n_samples < 0) return CAC_ERR_INVALID;
-    return 1 + n_samples / plan->p.hop_length;
+    return frames_of(plan, n_samples);
 }
 
 extern "C" int32_t cac_spec_rows(const cac_spec_plan* plan) {
@@ -121,7 +152,7 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
         tab[i] = h_item_offset[i];
         tab[n_items + i] = h_item_samples[i];
         tab[2 * n_items + i] = total;
-        total += 1 + h_item_samples[i] / plan->p.hop_length;
+        total += frames_of(plan, h_item_samples[i]);
     }
     tab[3 * n_items] = total;
     int rc = ensure_cap(&plan->d_tab, &plan->tab_cap, tab.size() * sizeof(long long));
@@ -152,7 +183,8 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
     a.n_groups = plan->mb.n_groups;
     a.pbuf_len = plan->mb.pbuf_len;
     for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
-    CUDA_TRY(launch_spec4800(a, st));
+    if (plan->dft) CUDA_TRY(launch_band_dft(a, plan->d_tw, st));
+    else CUDA_TRY(launch_spec4800(a, st));
     return CAC_OK;
 }
 

@@ -346,6 +346,11 @@ void spec4800_host_tables(int n_fft, int kmin, float2* ltab, float2* rtab) {
     }
 }
 
+bool spec4800_supported(int n_fft) {
+    return n_fft == 4800 || n_fft == 1600 || n_fft == 3200 || n_fft == 4096 || n_fft == 2048 || n_fft == 1024 ||
+           n_fft == 512;
+}
+
 size_t spec4800_smem_bytes(const SpecArgs& a) {
     return (size_t)smem48_layout(a.n_fft / 64, a.n_mels, a.n_taps, a.pbuf_len).total;
 }
@@ -353,10 +358,16 @@ size_t spec4800_smem_bytes(const SpecArgs& a) {
 cudaError_t launch_spec4800(const SpecArgs& a, cudaStream_t st) {
     const size_t smem = spec4800_smem_bytes(a);
     void (*kern)(const SpecArgs) = nullptr;
-    if (a.n_fft == 4800) kern = spec4800_kernel<75>;
-    else if (a.n_fft == 1600) kern = spec4800_kernel<25>;
-    else if (a.n_fft == 4096) kern = spec4800_kernel<64>;   // signal_noise's full spectrum (src/identify_tracks.py:652-654)
-    else return cudaErrorInvalidValue;
+    switch (a.n_fft) {
+        case 4800: kern = spec4800_kernel<75>; break;   // sr // 10 at 48 kHz (get_end, morepork)
+        case 1600: kern = spec4800_kernel<25>; break;   // sr // 10 at 16 kHz
+        case 3200: kern = spec4800_kernel<50>; break;   // sr // 10 at 32 kHz
+        case 4096: kern = spec4800_kernel<64>; break;   // signal_noise's full spectrum (src/identify_tracks.py:652-654)
+        case 2048: kern = spec4800_kernel<32>; break;   // load_samples with a model whose metadata sets n_fft
+        case 1024: kern = spec4800_kernel<16>; break;
+        case 512:  kern = spec4800_kernel<8>; break;
+        default: return cudaErrorInvalidValue;
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int dev = 0, sms = 148;

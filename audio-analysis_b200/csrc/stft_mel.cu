@@ -515,6 +515,49 @@ __global__ void __launch_bounds__(256) normalize_rows_kernel(const float* __rest
     for (int i = threadIdx.x; i < row_len; i += 256) q[i] = normalize_sample(p[i], mn, range);
 }
 
+// ---- general-parameter path: the segments as dense rows -------------------------------------------
+// For parameter sets the fused kernel does not cover (n_fft other than 4096, bands above bin 1023) every
+// segment is written out zero-padded (np.pad, src/identify_tracks.py:165-168) and normalised in
+// normalize_data's exact float32 op order (:202-209); the rows then go through the framed-spectrum kernel
+// of stft4800.cu with its banded mel epilogue and through power_to_db_kernel (cac_api.cu).
+__global__ void __launch_bounds__(256) segment_rows_kernel(const float* __restrict__ pcm,
+                                                           const cac_segment* __restrict__ segs,
+                                                           float* __restrict__ rows, int seg_len, int normalize) {
+    __shared__ float smn[8], smx[8];
+    __shared__ float s_mn, s_range;
+    const long long seg = blockIdx.x;
+    const cac_segment sd = segs[seg];
+    const float* p = pcm + sd.pcm_offset;
+    float* q = rows + seg * seg_len;
+    float mn = 0.f, range = 1.f;
+    if (normalize) {
+        float lo = INFINITY, hi = -INFINITY;
+        for (int i = threadIdx.x; i < sd.n_valid; i += 256) { const float v = p[i]; lo = fminf(lo, v); hi = fmaxf(hi, v); }
+        lo = warp_min(lo); hi = warp_max(hi);
+        if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = lo; smx[threadIdx.x >> 5] = hi; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; ++w) { lo = fminf(lo, smn[w]); hi = fmaxf(hi, smx[w]); }
+            if (sd.n_valid < seg_len) { lo = fminf(lo, 0.f); hi = fmaxf(hi, 0.f); }   // the np.pad zeros
+            s_mn = lo; s_range = __fsub_rn(hi, lo);
+        }
+        __syncthreads();
+        mn = s_mn; range = s_range;
+    }
+    for (int j = threadIdx.x; j < seg_len; j += 256) {
+        const int r = j - sd.pad_left;
+        const float v = (r >= 0 && r < sd.n_valid) ? p[r] : 0.f;
+        q[j] = normalize ? normalize_sample(v, mn, range) : v;
+    }
+}
+
+// item tables of the framed-spectrum kernel for n equal rows: [offset | length | frame prefix sum]
+__global__ void item_table_kernel(long long* tab, long long n, int seg_len, int n_frames) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) { tab[i] = i * seg_len; tab[n + i] = seg_len; tab[2 * n + i] = i * n_frames; }
+    if (i == n) tab[3 * n] = n * n_frames;
+}
+
 // ---- custommel.mel_spec on a caller-supplied magnitude matrix [bins, frames] ----------------
 __global__ void __launch_bounds__(256) mel_project_kernel(const float* __restrict__ mag, float* __restrict__ out,
                                                           int n_frames, int n_mels, int power) {
@@ -584,6 +627,13 @@ cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStre
         const long long item = (long long)a.n_mels * a.n_frames;
         launch_db(a.out, a.out, a.segmax, a.n_segs, item, st);
     }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_segment_rows(const float* pcm, const cac_segment* segs, long long n, float* rows, int seg_len,
+                                int n_frames, int normalize, long long* tab, cudaStream_t st) {
+    segment_rows_kernel<<<(unsigned)n, 256, 0, st>>>(pcm, segs, rows, seg_len, normalize);
+    item_table_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, st>>>(tab, n, seg_len, n_frames);
     return cudaGetLastError();
 }
 

@@ -354,7 +354,7 @@ class SpecPlan:
             pass
 
     def frame_count(self, n_samples):
-        return 1 + int(n_samples) // self.hop_length
+        return int(lib.cac_spec_frame_count(self._h, int(n_samples)))   # librosa's count, also for odd n_fft
 
     def run(self, pcm, item_offset, item_samples, out=None, want_max=False):
         """pcm: flat CUDA float32 tensor.  Returns (out, frame_base[, max tensor]); `out` is a flat
@@ -365,7 +365,8 @@ class SpecPlan:
         ns = np.ascontiguousarray(item_samples, dtype=np.int64)
         assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
         assert off.shape == ns.shape and (off + ns <= pcm.numel()).all()
-        base = np.concatenate([[0], np.cumsum(1 + ns // self.hop_length)]).astype(np.int64)
+        n_fft = self.params.n_fft                               # 1 + (n + 2 (n_fft // 2) - n_fft) // hop frames each
+        base = np.concatenate([[0], np.cumsum(np.maximum(0, 1 + (ns + 2 * (n_fft // 2) - n_fft) // self.hop_length))]).astype(np.int64)
         total = int(base[-1])
         if out is None:
             out = torch.empty((total * self.rows,), dtype=torch.float32, device=dev)

@@ -37,7 +37,10 @@ typedef enum cac_status {
  * (src/identify_tracks.py:65-86). */
 typedef struct cac_params {
     int32_t sample_rate;     /* sr, 48000 after load_recording (src/identify_tracks.py:49-57) */
-    int32_t n_fft;           /* 4096 (src/identify_tracks.py:85) */
+    int32_t n_fft;           /* 4096 (src/identify_tracks.py:85) unless the model's metadata sets it (:493): the fused
+                              * kernel serves 4096 with bands below bin 1024; 4096 with higher bands, 2048, 1024, 512,
+                              * 4800, 3200 and 1600 run unfused (segment rows -> framed spectrum + mel -> dB); any
+                              * other length makes cac_features_run fail with CAC_ERR_INVALID */
     int32_t hop_length;      /* 281 default of load_samples (:71); 640 classify fallback (:474) */
     int32_t n_mels;          /* 160 */
     int32_t segment_samples; /* int(sr * segment_length) (:109) */
@@ -76,7 +79,7 @@ int cac_plan_frames(const cac_plan* plan);
  * waits for that kernel and returns its duration. */
 int cac_plan_set_profiling(cac_plan* plan, int enable);
 int cac_plan_last_kernel_ms(cac_plan* plan, float* ms);
-/* Bytes of device scratch cac_features_run needs for n_segments. */
+/* Bytes of device scratch cac_features_run needs for n_segments (the unfused path adds the normalised segment rows). */
 size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
 
 /* load_samples' inner loop (src/identify_tracks.py:163-190) for n_segments segments at once:
@@ -152,7 +155,10 @@ int cac_ci_entries_run(cac_ci_plan* plan, const uint8_t* d_points, const int64_t
  * padding, 1 + len // hop frames) followed by |.|**power, restricted to the FFT bins the caller
  * consumes, optionally projected through a custommel.mel_f filterbank. */
 typedef struct cac_spec_params {
-    int32_t n_fft;        /* 4800 = int(sr / 10) at 48 kHz (src/identify_morepork.py:23, src/identify_tracks.py:389) */
+    int32_t n_fft;        /* 4800 = int(sr / 10) at 48 kHz (src/identify_morepork.py:23, src/identify_tracks.py:389).
+                           * Mixed-radix kernel: 4800, 3200, 1600, 4096, 2048, 1024, 512.  Any other length up to 19,000,
+                           * even or odd (4410 at 44.1 kHz, 2205 at 22.05 kHz, ...): raw bands of at most 512 bins by a
+                           * direct band DFT (band_dft.cu) - what _load_sample needs at the file's native rate (:20-25) */
     int32_t hop_length;   /* int(n_fft / 2) for morepork (:24); 281 for get_end (:388) */
     int32_t bin_lo;       /* raw output (n_mels == 0): FFT bins [bin_lo, bin_hi); morepork 60:120 (:25) */
     int32_t bin_hi;
@@ -165,7 +171,7 @@ typedef struct cac_spec_plan cac_spec_plan;
 int cac_spec_plan_create(const cac_spec_params* params, const float* h_mel_weights, int device,
                          cac_spec_plan** out);
 int cac_spec_plan_destroy(cac_spec_plan* plan);
-/* 1 + n_samples // hop_length */
+/* librosa's frame count: 1 + (n_samples + 2 (n_fft // 2) - n_fft) // hop_length (= 1 + n_samples // hop_length for even n_fft) */
 int64_t cac_spec_frame_count(const cac_spec_plan* plan, int64_t n_samples);
 /* rows per frame of the output: n_mels, or bin_hi - bin_lo */
 int32_t cac_spec_rows(const cac_spec_plan* plan);

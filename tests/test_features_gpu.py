@@ -151,8 +151,8 @@ def test_error_paths(engine):
     rc = engine.lib.cac_plan_create(ctypes.byref(p), w.ctypes.data_as(ctypes.c_void_p), 0, ctypes.byref(h))
     assert rc == -1 and b"power" in engine.lib.cac_last_error()
     from audio_analysis_b200 import custommel
-    wide = custommel.mel_f(48000, 160, 50, 20000, 4096, 1750)
-    plan = engine.FeaturePlan(wide, 48000, 4096, 281, 160, 144000)
+    odd = custommel.mel_f(48000, 160, 50, 11000, 3000, 1750)    # a frame length no kernel is built for
+    plan = engine.FeaturePlan(odd, 48000, 3000, 281, 160, 144000)
     with pytest.raises(engine.CacError):
         plan.run_host(np.zeros(144000, np.float32), np.array([(0, 144000, 0)], dtype=engine.SEGMENT_DTYPE))
     good = engine.FeaturePlan(custommel.mel_f(48000, 160, 50, 11000, 4096, 1750), 48000, 4096, 281, 160, 144000)
@@ -266,6 +266,46 @@ def test_parameter_sweep_vs_oracle(engine, hop, n_mels, brk, fmin, fmax, power, 
                 n_ok += int(np.sum(np.abs(g - r) <= 1e-4 * np.abs(r) + 1e-30))
     if not db:
         assert n_ok >= 0.999 * n_cells
+
+
+@pytest.mark.parametrize("n_fft,hop,n_mels,fmax,power,db,norm", [
+    (2048, 281, 160, 11000, 2, True, True),       # a model whose metadata sets n_fft (src/identify_tracks.py:493)
+    (1024, 256, 80, 11000, 2, True, False),
+    (512, 128, 40, 8000, 1, False, True),
+    (4096, 281, 160, 16000, 2, True, True),       # bands above bin 1023: outside the fused kernel's range
+])
+def test_general_path_other_frame_lengths_vs_oracle(engine, n_fft, hop, n_mels, fmax, power, db, norm):
+    """Parameter sets the fused kernel does not cover go through segment rows -> framed-spectrum kernel with
+    mel epilogue -> power_to_db (cac_plan general path) behind the same load_samples call."""
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(900 + n_fft // 64, seconds=6.0)
+    tracks = [(0.0, 6.0, 0, 24000), (0.5, 1.4, 700, 2500), (4.6, 6.0, 1000, 4000)]
+    kw = dict(hop_length=hop, mel_break=1750, n_mels=n_mels, fmin=50, fmax=fmax, power=power, db_scale=db,
+              normalize=norm, n_fft=n_fft)
+    np.random.seed(5)
+    got = T.load_samples(rec, 48000, [T.Signal(*t) for t in tracks], 3.0, 1.5, **kw)
+    np.random.seed(5)
+    ref = O.load_samples(rec, 48000, [O.Signal(*t) for t in tracks], 3.0, 1.5, **kw)
+    assert [len(g) for g in got] == [len(r) for r in ref]
+    n_cells = n_ok = 0
+    for g_track, r_track in zip(got, ref):
+        for g, r in zip(g_track, r_track):
+            r = np.asarray(r)
+            assert g.shape == r.shape == (n_mels, 1 + 144000 // hop, 1)
+            if db:
+                assert np.abs(g - r).max() <= 1e-2
+            else:
+                n_cells += r.size
+                n_ok += int(np.sum(np.abs(g - r) <= 1e-4 * np.abs(r) + 1e-30))
+    if not db:
+        assert n_ok >= 0.999 * n_cells
+
+
+def test_unsupported_frame_length_fails_loudly(engine):
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(1, seconds=3.0)
+    with pytest.raises(engine.CacError):
+        T.load_samples(rec, 48000, [T.Signal(0.0, 3.0, 0, 24000)], 3.0, 1.5, n_fft=3000, **{k: v for k, v in S1.items() if k != "n_fft"})
 
 
 def test_pcm16_host_path_equals_float_path(engine):

@@ -50,6 +50,25 @@ def test_morepork_short_recordings_and_wraparound_slices(engine, n):
     assert np.abs(samples - ref).max() <= 1.25e-4
 
 
+@pytest.mark.parametrize("sr,seconds", [(32000, 7.0), (44100, 6.5), (22050, 9.0), (8000, 12.0)])
+def test_morepork_other_native_rates_vs_oracle(engine, sr, seconds):
+    """_load_sample keeps the file's own rate (librosa.load(sr=None), src/identify_morepork.py:20): 32 kHz runs on the
+    mixed-radix kernel (n_fft 3200), the rates whose n_fft = int(sr / 10) has other prime factors or is odd
+    (4410, 2205 with hop 1102, 800) on the direct band DFT (band_dft.cu)."""
+    from audio_analysis_b200 import identify_morepork as M
+    rec = synth.recording(4000 + sr // 100, seconds=seconds, sr=sr)
+    ref_spec = O.morepork_spectrogram(rec, sr)
+    got_sr, spec = M._load_sample((rec, sr))
+    assert got_sr == sr
+    frac = _check_mag(spec, ref_spec)
+    samples, starts = M.samples_from_recording((rec, sr))
+    ref, ref_starts = O.morepork_windows(ref_spec)
+    assert samples.shape == ref.shape and list(starts) == list(ref_starts)
+    d = np.abs(samples - ref)
+    print("morepork %d Hz: spec match@1e-4 %.5f, window max diff %.3e" % (sr, frac, d.max()))
+    assert d.max() <= 1.25e-4
+
+
 def test_morepork_batch_equals_single(engine):
     import torch
     from audio_analysis_b200 import identify_morepork as M
@@ -113,8 +132,10 @@ def test_spec_plan_raw_layouts_and_max(engine):
 
 
 def test_spec_plan_rejects_unsupported(engine):
-    with pytest.raises(engine.CacError):
-        engine.SpecPlan(4410, 2205, bin_lo=60, bin_hi=120)
+    with pytest.raises(engine.CacError):      # the direct band DFT serves raw bands only, not a mel epilogue
+        engine.SpecPlan(4410, 281, n_mels=120, power=1, mel_weights=np.ones((120, 2206), np.float32))
+    with pytest.raises(engine.CacError):      # ... and not more than 512 bins
+        engine.SpecPlan(4410, 2205, bin_lo=0, bin_hi=2206)
     with pytest.raises(engine.CacError):
         engine.SpecPlan(4800, 2400, bin_lo=100, bin_hi=3000)
 
