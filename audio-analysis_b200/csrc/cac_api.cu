@@ -360,7 +360,10 @@ static int features_host_impl(cac_plan* plan, const void* h_pcm_any, bool pcm16,
     const int n_chunks = (int)std::min<int64_t>(256, std::max<int64_t>(1, (n + 77) / 156));
     const int64_t per_chunk = (n + n_chunks - 1) / n_chunks;
     const size_t work_chunk = (cac_features_work_bytes(plan, per_chunk) + 255) / 256 * 256;
-    if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, work_chunk * n_chunks))) return rc;
+    // the general path's scratch holds whole segment rows: its chunks run one after the other on the compute stream,
+    // so they share one slice instead of n_chunks of them
+    const size_t work_slices = plan->general ? 1 : (size_t)n_chunks;
+    if ((rc = ensure_cap(&plan->d_work, &plan->work_cap, work_chunk * work_slices))) return rc;
     if (!plan->s_h2d) {
         CUDA_TRY(cudaStreamCreateWithFlags(&plan->s_h2d, cudaStreamNonBlocking));
         CUDA_TRY(cudaStreamCreateWithFlags(&plan->s_comp, cudaStreamNonBlocking));
@@ -401,7 +404,7 @@ static int features_host_impl(cac_plan* plan, const void* h_pcm_any, bool pcm16,
         if (s1 <= s0) break;
         CUDA_TRY(cudaStreamWaitEvent(plan->s_comp, plan->ev_up[c], 0));
         if ((rc = cac_features_run(plan, plan->d_pcm, plan->d_segs + s0, s1 - s0, plan->d_out + s0 * item,
-                                   (char*)plan->d_work + work_chunk * c, plan->s_comp)))
+                                   (char*)plan->d_work + work_chunk * (plan->general ? 0 : c), plan->s_comp)))
             return rc;
         CUDA_TRY(cudaEventRecord(plan->ev_done[c], plan->s_comp));
         CUDA_TRY(cudaStreamWaitEvent(plan->s_d2h, plan->ev_done[c], 0));

@@ -18,28 +18,34 @@ constexpr int kWarps48 = 8;
 constexpr int kExStride48 = 33;                         // float2 per row of the Z matrix (odd: conflict-free)
 
 // z[I] = (x[2n] w[2n], x[2n+1] w[2n+1]), n = lane + 32 I; w[s] = 0.5 - 0.5 cos(2 pi s / (64 R)), s = 64 I + (2 lane + e)
-template <int R, int I>
+// MODE 1: the whole frame lies inside the recording and is 8-byte aligned (64-bit loads at immediate offsets from
+// one base pointer); MODE 2: inside but not aligned (odd hop: every other frame) - two 32-bit loads, no checks;
+// MODE 0: every sample is bounds-checked (the centre-padded frames at both ends of a recording).  The case is
+// decided once per frame, outside the unrolled sequence (a per-element branch costs more than the load it guards).
+template <int R, int I, int MODE>
 struct Load48 {
-    static __device__ __forceinline__ void run(float (&re)[R], float (&im)[R], const float* p, long long t0,
-                                               long long n, bool fast, int lane, float hcb0, float hsb0, float hcb1,
-                                               float hsb1) {
+    static __device__ __forceinline__ void run(float (&re)[R], float (&im)[R], const float* pl, long long tl,
+                                               long long n, float hcb0, float hsb0, float hcb1, float hsb1) {
+        // pl = p + 2 lane, tl = t0 + 2 lane: sample index of this lane's first element
         constexpr float ca = (float)cx_cos2pi(I, R);
         constexpr float sa = (float)cx_sin2pi(I, R);
         const float w0 = fmaf(-ca, hcb0, fmaf(sa, hsb0, 0.5f));
         const float w1 = fmaf(-ca, hcb1, fmaf(sa, hsb1, 0.5f));
-        const int s = 2 * (lane + 32 * I);
         float x0, x1;
-        if (fast) {
-            const float2 v = __ldg(reinterpret_cast<const float2*>(p + s));
+        if constexpr (MODE == 1) {
+            const float2 v = __ldg(reinterpret_cast<const float2*>(pl + 64 * I));
             x0 = v.x; x1 = v.y;
+        } else if constexpr (MODE == 2) {
+            x0 = __ldg(pl + 64 * I);
+            x1 = __ldg(pl + 64 * I + 1);
         } else {
-            const long long a0 = t0 + s;
-            x0 = (a0 >= 0 && a0 < n) ? __ldg(p + s) : 0.f;
-            x1 = (a0 + 1 >= 0 && a0 + 1 < n) ? __ldg(p + s + 1) : 0.f;
+            const long long a0 = tl + 64 * I;
+            x0 = (a0 >= 0 && a0 < n) ? __ldg(pl + 64 * I) : 0.f;
+            x1 = (a0 + 1 >= 0 && a0 + 1 < n) ? __ldg(pl + 64 * I + 1) : 0.f;
         }
         re[I] = x0 * w0;
         im[I] = x1 * w1;
-        if constexpr (I + 1 < R) Load48<R, I + 1>::run(re, im, p, t0, n, fast, lane, hcb0, hsb0, hcb1, hsb1);
+        if constexpr (I + 1 < R) Load48<R, I + 1, MODE>::run(re, im, pl, tl, n, hcb0, hsb0, hcb1, hsb1);
     }
 };
 
@@ -127,8 +133,13 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
     const long long stride = (long long)gridDim.x * kWarps48;
     float vmax = 0.f;
 
+    // The frame body is ~5,000 straight-line instructions (80 KB), far beyond the instruction caches: the CTA's
+    // warps start every frame together so that they walk the code at the same time and share one fetch stream.
 #pragma unroll 1
-    for (long long g = (long long)blockIdx.x * kWarps48 + warp; g < a.n_frames_total; g += stride) {
+    for (long long g0 = (long long)blockIdx.x * kWarps48; g0 < a.n_frames_total; g0 += stride) {
+        __syncthreads();
+        const long long g = g0 + warp;
+        if (g >= a.n_frames_total) continue;
         int lo = 0, hi = a.n_items - 1;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
@@ -140,11 +151,14 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
         const long long n = a.item_len[lo];
         const long long t0 = (long long)f * a.hop - kHalf;                // centre = True
         const float* p = a.pcm + a.item_off[lo] + t0;
-        const bool fast = t0 >= 0 && t0 + 2 * kHalf <= n && ((reinterpret_cast<uintptr_t>(p) & 7) == 0);
+        const bool inside = t0 >= 0 && t0 + 2 * kHalf <= n;
+        const bool aligned = (reinterpret_cast<uintptr_t>(p) & 7) == 0;
         {
             float re[R], im[R];
             const float2 h0 = lt[18 * 32], h1 = lt[19 * 32];
-            Load48<R, 0>::run(re, im, p, t0, n, fast, lane, h0.x, h0.y, h1.x, h1.y);
+            if (inside && aligned) Load48<R, 0, 1>::run(re, im, p + 2 * lane, t0 + 2 * lane, n, h0.x, h0.y, h1.x, h1.y);
+            else if (inside) Load48<R, 0, 2>::run(re, im, p + 2 * lane, t0 + 2 * lane, n, h0.x, h0.y, h1.x, h1.y);
+            else Load48<R, 0, 0>::run(re, im, p + 2 * lane, t0 + 2 * lane, n, h0.x, h0.y, h1.x, h1.y);
             fft_dif<R>(re, im);
             __syncwarp();                                                 // previous frame's readers are done
             Tw48<R, 0>::run(re, im, lt, ex + lane);

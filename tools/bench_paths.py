@@ -88,8 +88,34 @@ def bench_morepork(n_rec=4096):
                       "hbm_frac_of_measured": algo / ms / 1e6 / PEAK, "dtype": "f32"}), flush=True)
 
 
+def bench_hop281(n_rec=64):
+    """The two whole-recording spectra of identify_tracks.classify (src/identify_tracks.py:419-420): get_end's
+    120-mel magnitude spectrogram (n_fft 4800, hop 281) and signal_noise's full magnitude spectrum (n_fft 4096,
+    hop 281, [2049, frames] per recording), device-resident, n_rec one-minute recordings per launch."""
+    from audio_analysis_b200 import engine, custommel
+    pool = np.stack([synth.recording(500 + i, 60.0, 48000) for i in range(16)])
+    n_rec = int(os.environ.get("CAC_HOP281_RECORDINGS", n_rec))
+    reps = (n_rec + len(pool) - 1) // len(pool)
+    pcm = torch.from_numpy(pool).cuda().repeat(reps, 1)[:n_rec].contiguous()
+    n = pcm.shape[1]
+    offs, lens = np.arange(n_rec, dtype=np.int64) * n, np.full(n_rec, n, dtype=np.int64)
+    w = custommel._mel_f_cached(48000, 120, 50, 11000, 4800, 1750)
+    plans = {"get_end_mel_spectrogram": engine.SpecPlan(4800, 281, n_mels=120, power=1, mel_weights=w),
+             "signal_noise_spectrum": engine.SpecPlan(4096, 281, bin_lo=0, bin_hi=2049, n_mels=0, power=1, bin_major=True)}
+    for name, plan in plans.items():
+        out = plan.run(pcm.view(-1), offs, lens)[0]
+        ms = timed(lambda: plan.run(pcm.view(-1), offs, lens, out=out), steps=5)
+        algo = pcm.numel() * 4 + out.numel() * 4
+        print(json.dumps({"path": name, "recordings": n_rec, "ms": ms, "recording_hours_per_s": n_rec / 60.0 / (ms * 1e-3),
+                          "algorithmic_GBps": algo / ms / 1e6, "hbm_frac_of_measured": algo / ms / 1e6 / PEAK,
+                          "dtype": "f32"}), flush=True)
+        del out
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["ci"]
+    if "hop281" in which:
+        bench_hop281()
     if "ci" in which:
         bench_ci()
     if "morepork" in which:
