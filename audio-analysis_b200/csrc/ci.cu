@@ -125,13 +125,14 @@ struct CiUntangle {
 
 // load z[lane + 32*I]: I < 16 from the float4 at m = lane + 32 I as (x0*w, x2*w); I >= 16 from the float4
 // at m' = (31 - lane) + 32 (31 - I) as (x3*w, x1*w)   (Makhoul reorder folded into the complex packing)
-template <int I>
+// ALIGNED is decided once per window, outside the unrolled sequence
+template <int I, bool ALIGNED>
 struct CiLoad {
-    static __device__ __forceinline__ void run(double (&zr)[32], double (&zi)[32], const float* p, bool aligned,
+    static __device__ __forceinline__ void run(double (&zr)[32], double (&zi)[32], const float* p,
                                                const double2* wz, const double2* wz2, int lane) {
         const int m = (I < 16) ? lane + 32 * I : (31 - lane) + 32 * (31 - I);
         float4 f;
-        if (aligned) {
+        if constexpr (ALIGNED) {
             f = __ldg(reinterpret_cast<const float4*>(p) + m);
         } else {
             f.x = __ldg(p + 4 * m); f.y = __ldg(p + 4 * m + 1); f.z = __ldg(p + 4 * m + 2); f.w = __ldg(p + 4 * m + 3);
@@ -145,7 +146,7 @@ struct CiLoad {
             zr[I] = (double)f.w * w.x;
             zi[I] = (double)f.y * w.y;
         }
-        if constexpr (I + 1 < 32) CiLoad<I + 1>::run(zr, zi, p, aligned, wz, wz2, lane);
+        if constexpr (I + 1 < 32) CiLoad<I + 1, ALIGNED>::run(zr, zi, p, wz, wz2, lane);
     }
 };
 
@@ -181,7 +182,8 @@ __global__ void __launch_bounds__(kCiWarps * 32, 1) ci_bins_kernel(const CiArgs 
         const bool aligned = ((reinterpret_cast<uintptr_t>(p) & 15) == 0);
 
         double zr[32], zi[32];
-        CiLoad<0>::run(zr, zi, p, aligned, wz, wz2, lane);
+        if (aligned) CiLoad<0, true>::run(zr, zi, p, wz, wz2, lane);
+        else CiLoad<0, false>::run(zr, zi, p, wz, wz2, lane);
         fft_dif<32>(zr, zi);
         CiTw1<0>::run(zr, zi, lt);
         __syncwarp();
