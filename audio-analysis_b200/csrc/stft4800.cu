@@ -133,13 +133,8 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
     const long long stride = (long long)gridDim.x * kWarps48;
     float vmax = 0.f;
 
-    // The frame body is ~5,000 straight-line instructions (80 KB), far beyond the instruction caches: the CTA's
-    // warps start every frame together so that they walk the code at the same time and share one fetch stream.
 #pragma unroll 1
-    for (long long g0 = (long long)blockIdx.x * kWarps48; g0 < a.n_frames_total; g0 += stride) {
-        __syncthreads();
-        const long long g = g0 + warp;
-        if (g >= a.n_frames_total) continue;
+    for (long long g = (long long)blockIdx.x * kWarps48 + warp; g < a.n_frames_total; g += stride) {
         int lo = 0, hi = a.n_items - 1;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
