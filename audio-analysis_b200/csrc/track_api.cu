@@ -40,17 +40,19 @@ extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t 
     keep_pool_warm();
     Scratch s(st);
     float *d_t, *d_med;
-    unsigned char *m0, *m1, *m2;
     int* d_small;
+    const size_t wpr = (size_t)((cols + 31) / 32), nw = (size_t)rows * wpr;
     // d_t doubles as the label array later (same size: 4 bytes per cell)
     CUDA_TRY(cudaMallocAsync(&s.p[0], n * sizeof(float), st));
     CUDA_TRY(cudaMallocAsync(&s.p[1], n * sizeof(int), st));
-    CUDA_TRY(cudaMallocAsync(&s.p[2], 3 * n, st));
+    CUDA_TRY(cudaMallocAsync(&s.p[2], 3 * nw * sizeof(unsigned), st));
     CUDA_TRY(cudaMallocAsync(&s.p[3], ((size_t)rows + cols) * sizeof(float), st));
     CUDA_TRY(cudaMallocAsync(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int), st));
     d_t = (float*)s.p[0];
     int* d_rootid = (int*)s.p[1];
-    m0 = (unsigned char*)s.p[2]; m1 = m0 + n; m2 = m1 + n;
+    unsigned* m0 = (unsigned*)s.p[2];              // bit-packed masks (track_bits.cu): 2.6 MB each for a one-minute recording
+    unsigned* m1 = m0 + nw;
+    unsigned* m2 = m1 + nw;
     d_med = (float*)s.p[3];
     d_small = (int*)s.p[4];
     float* rowmed = d_med;
@@ -60,19 +62,19 @@ extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t 
     CUDA_TRY(launch_row_median(d_spec, rowmed, rows, cols, st));
     CUDA_TRY(launch_transpose(d_spec, d_t, rows, cols, st));
     CUDA_TRY(launch_row_median(d_t, colmed, cols, rows, st));
-    CUDA_TRY(launch_signal_mask(d_spec, rowmed, colmed, m0, rows, cols, st));
-    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks, m0, n, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(launch_signal_mask_bits(d_spec, rowmed, colmed, m0, rows, cols, st));
+    if (d_stage_masks) CUDA_TRY(launch_unpack_bits(m0, d_stage_masks, rows, cols, st));
     // cv2.morphologyEx(MORPH_OPEN, ones((4, 4))) = erode then dilate (:669-671)
-    CUDA_TRY(launch_morph_rect(m0, m1, m2, rows, cols, 4, 4, false, st));
-    CUDA_TRY(launch_morph_rect(m2, m1, m0, rows, cols, 4, 4, true, st));
-    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks + n, m0, n, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(launch_morph_rect_bits(m0, m1, m2, rows, cols, 4, 4, false, st));
+    CUDA_TRY(launch_morph_rect_bits(m2, m1, m0, rows, cols, 4, 4, true, st));
+    if (d_stage_masks) CUDA_TRY(launch_unpack_bits(m0, d_stage_masks + n, rows, cols, st));
     // cv2.dilate(ones((height, width))) then cv2.erode(ones((height // 10, width))) (:683-684)
-    CUDA_TRY(launch_morph_rect(m0, m1, m2, rows, cols, dilate_h, dilate_w, true, st));
-    CUDA_TRY(launch_morph_rect(m2, m1, m0, rows, cols, erode_h, dilate_w, false, st));
-    if (d_stage_masks) CUDA_TRY(cudaMemcpyAsync(d_stage_masks + 2 * n, m0, n, cudaMemcpyDeviceToDevice, st));
-    // cv2.connectedComponentsWithStats (8-connectivity) (:686)
+    CUDA_TRY(launch_morph_rect_bits(m0, m1, m2, rows, cols, dilate_h, dilate_w, true, st));
+    CUDA_TRY(launch_morph_rect_bits(m2, m1, m0, rows, cols, erode_h, dilate_w, false, st));
+    if (d_stage_masks) CUDA_TRY(launch_unpack_bits(m0, d_stage_masks + 2 * n, rows, cols, st));
+    // cv2.connectedComponentsWithStats (8-connectivity) (:686), on horizontal runs
     int* d_stats = d_small + 4;
-    CUDA_TRY(launch_ccl(m0, (int*)d_t, d_rootid, rows, (int)cols, d_small, d_stats, max_components, st));
+    CUDA_TRY(launch_ccl_runs(m0, (int*)d_t, d_rootid, rows, (int)cols, d_small, d_stats, max_components, st));
     int count = 0;
     CUDA_TRY(cudaMemcpyAsync(&count, d_small, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));

@@ -1,8 +1,6 @@
-// signal_noise after its STFT (src/identify_tracks.py:658-691): exact row / column medians of the
-// normalised magnitude spectrogram, the 3x-median mask, cv2-compatible rectangular morphology
-// (4x4 open, dilate (height, width), erode (height // 10, width)) and 8-connected components with
-// bounding boxes.  Everything is small integer / byte work on a [2049 x frames] matrix that is
-// already resident in HBM (84 MB per minute, mostly L2-resident): plain coalesced kernels.
+// signal_noise after its STFT (src/identify_tracks.py:658-666): exact row / column medians of the
+// normalised magnitude spectrogram ([2049 x frames], 84 MB per minute, mostly L2-resident).  The mask,
+// morphology and connected-component stages that follow (:667-686) work on a bit-packed mask: track_bits.cu.
 #include "cac_common.cuh"
 #include "track_signals.cuh"
 
@@ -75,138 +73,6 @@ __global__ void __launch_bounds__(256) row_median_kernel(const float* __restrict
     }
 }
 
-// ---- signal = (spec > 3 * column_medians) & (spec > 3 * row_medians)  (:667) ---------------------
-__global__ void __launch_bounds__(256) signal_mask_kernel(const float* __restrict__ spec, const float* __restrict__ rowmed,
-                                                          const float* __restrict__ colmed, unsigned char* __restrict__ mask,
-                                                          int rows, long long cols) {
-    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
-    const int r = blockIdx.y;
-    if (c >= cols) return;
-    const float v = spec[(size_t)r * cols + c];
-    const float tc = __fmul_rn(3.0f, colmed[c]), tr = __fmul_rn(3.0f, rowmed[r]);
-    mask[(size_t)r * cols + c] = (v > tc && v > tr) ? 1 : 0;
-}
-
-// ---- cv2.erode / cv2.dilate with a rectangular all-ones kernel, separable passes -----------------
-// out(y, x) = min|max over d in [-anchor, k - 1 - anchor] of in(.. + d), pixels outside the image ignored
-// (cv2's default border value for morphology); anchor = k / 2 (cv2's default centre).
-template <bool IS_MAX>
-__global__ void __launch_bounds__(256) morph_h_kernel(const unsigned char* __restrict__ in, unsigned char* __restrict__ out,
-                                                      int rows, long long cols, int k) {
-    extern __shared__ unsigned char seg[];          // 256 + k pixels of this row
-    const int anchor = k / 2;
-    const long long c0 = (long long)blockIdx.x * 256;
-    const int r = blockIdx.y;
-    const unsigned char* row = in + (size_t)r * cols;
-    const unsigned char neutral = IS_MAX ? 0 : 255;
-    for (int i = threadIdx.x; i < 256 + k; i += 256) {
-        const long long c = c0 - anchor + i;
-        seg[i] = (c >= 0 && c < cols) ? row[c] : neutral;
-    }
-    __syncthreads();
-    const long long c = c0 + threadIdx.x;
-    if (c >= cols) return;
-    unsigned char v = neutral;
-    for (int d = 0; d < k; ++d) {
-        const unsigned char s = seg[threadIdx.x + d];
-        v = IS_MAX ? max(v, s) : min(v, s);
-    }
-    out[(size_t)r * cols + c] = v;
-}
-
-template <bool IS_MAX>
-__global__ void __launch_bounds__(256) morph_v_kernel(const unsigned char* __restrict__ in, unsigned char* __restrict__ out,
-                                                      int rows, long long cols, int k) {
-    const int anchor = k / 2;
-    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
-    const int r = blockIdx.y;
-    if (c >= cols) return;
-    unsigned char v = IS_MAX ? 0 : 255;
-    for (int d = 0; d < k; ++d) {
-        const int rr = r - anchor + d;
-        if (rr >= 0 && rr < rows) {
-            const unsigned char s = in[(size_t)rr * cols + c];
-            v = IS_MAX ? max(v, s) : min(v, s);
-        }
-    }
-    out[(size_t)r * cols + c] = v;
-}
-
-// ---- 8-connected components: union-find on pixel indices ------------------------------------------
-__device__ __forceinline__ int ccl_find(const int* label, int a) {
-    int p = label[a];
-    while (p != a) { a = p; p = label[a]; }
-    return a;
-}
-__device__ __forceinline__ void ccl_union(int* label, int a, int b) {
-    while (true) {
-        a = ccl_find(label, a);
-        b = ccl_find(label, b);
-        if (a == b) return;
-        if (a < b) { const int t = a; a = b; b = t; }     // a > b: hang the larger root under the smaller
-        const int old = atomicMin(&label[a], b);
-        if (old == a) return;
-        a = old;
-    }
-}
-
-__global__ void __launch_bounds__(256) ccl_init_kernel(const unsigned char* __restrict__ img, int* __restrict__ label,
-                                                       long long n) {
-    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (i < n) label[i] = img[i] ? (int)i : -1;
-}
-
-__global__ void __launch_bounds__(256) ccl_merge_kernel(const unsigned char* __restrict__ img, int* __restrict__ label,
-                                                        int rows, int cols) {
-    const int x = blockIdx.x * 256 + threadIdx.x;
-    const int y = blockIdx.y;
-    if (x >= cols) return;
-    const int p = y * cols + x;
-    if (!img[p]) return;
-    if (x > 0 && img[p - 1]) ccl_union(label, p, p - 1);
-    if (y > 0) {
-        const int q = p - cols;
-        if (img[q]) ccl_union(label, p, q);
-        if (x > 0 && img[q - 1]) ccl_union(label, p, q - 1);
-        if (x + 1 < cols && img[q + 1]) ccl_union(label, p, q + 1);
-    }
-}
-
-// roots get consecutive ids (arbitrary order); rootid[p] is valid for root pixels only
-__global__ void __launch_bounds__(256) ccl_roots_kernel(const int* __restrict__ label, int* __restrict__ rootid,
-                                                        long long n, int* __restrict__ counter, int max_components) {
-    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (i >= n || label[i] != (int)i) return;
-    const int id = atomicAdd(counter, 1);
-    rootid[i] = id < max_components ? id : -1;
-}
-
-// stats[id] = {min x, min y, max x, max y, area, first 2x2 block in raster order}
-__global__ void __launch_bounds__(256) ccl_stats_kernel(const int* __restrict__ label, const int* __restrict__ rootid,
-                                                        int rows, int cols, int* __restrict__ stats) {
-    const int x = blockIdx.x * 256 + threadIdx.x;
-    const int y = blockIdx.y;
-    if (x >= cols) return;
-    const int p = y * cols + x;
-    if (label[p] < 0) return;
-    const int id = rootid[ccl_find(label, p)];
-    if (id < 0) return;
-    int* s = stats + 6 * id;
-    atomicMin(s + 0, x);
-    atomicMin(s + 1, y);
-    atomicMax(s + 2, x);
-    atomicMax(s + 3, y);
-    atomicAdd(s + 4, 1);
-    atomicMin(s + 5, (y >> 1) * ((cols + 1) >> 1) + (x >> 1));
-}
-
-__global__ void __launch_bounds__(256) ccl_stats_init_kernel(int* stats, int max_components) {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i >= max_components) return;
-    int* s = stats + 6 * i;
-    s[0] = 0x7fffffff; s[1] = 0x7fffffff; s[2] = -1; s[3] = -1; s[4] = 0; s[5] = 0x7fffffff;
-}
-
 // ---- launchers --------------------------------------------------------------------------------------
 cudaError_t launch_transpose(const float* in, float* out, int rows, long long cols, cudaStream_t st) {
     dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
@@ -216,40 +82,6 @@ cudaError_t launch_transpose(const float* in, float* out, int rows, long long co
 
 cudaError_t launch_row_median(const float* in, float* out, long long rows, long long cols, cudaStream_t st) {
     row_median_kernel<<<(unsigned)rows, 256, 0, st>>>(in, out, cols);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_signal_mask(const float* spec, const float* rowmed, const float* colmed, unsigned char* mask, int rows,
-                               long long cols, cudaStream_t st) {
-    dim3 grid((unsigned)((cols + 255) / 256), (unsigned)rows);
-    signal_mask_kernel<<<grid, 256, 0, st>>>(spec, rowmed, colmed, mask, rows, cols);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_morph_rect(const unsigned char* in, unsigned char* tmp, unsigned char* out, int rows, long long cols,
-                              int kh, int kw, bool is_max, cudaStream_t st) {
-    dim3 grid((unsigned)((cols + 255) / 256), (unsigned)rows);
-    if (is_max) {
-        morph_h_kernel<true><<<grid, 256, 256 + kw, st>>>(in, tmp, rows, cols, kw);
-        morph_v_kernel<true><<<grid, 256, 0, st>>>(tmp, out, rows, cols, kh);
-    } else {
-        morph_h_kernel<false><<<grid, 256, 256 + kw, st>>>(in, tmp, rows, cols, kw);
-        morph_v_kernel<false><<<grid, 256, 0, st>>>(tmp, out, rows, cols, kh);
-    }
-    return cudaGetLastError();
-}
-
-cudaError_t launch_ccl(const unsigned char* img, int* label, int* rootid, int rows, int cols, int* counter, int* stats,
-                       int max_components, cudaStream_t st) {
-    const long long n = (long long)rows * cols;
-    dim3 grid((unsigned)((cols + 255) / 256), (unsigned)rows);
-    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), st);
-    if (e != cudaSuccess) return e;
-    ccl_stats_init_kernel<<<(max_components + 255) / 256, 256, 0, st>>>(stats, max_components);
-    ccl_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(img, label, n);
-    ccl_merge_kernel<<<grid, 256, 0, st>>>(img, label, rows, cols);
-    ccl_roots_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(label, rootid, n, counter, max_components);
-    ccl_stats_kernel<<<grid, 256, 0, st>>>(label, rootid, rows, cols, stats);
     return cudaGetLastError();
 }
 
