@@ -98,6 +98,20 @@ def _check_finite(first_values):
         raise ParameterError("Audio buffer is not finite everywhere")
 
 
+def _is_cuda(frames):
+    return hasattr(frames, "is_cuda") and frames.is_cuda
+
+
+def to_device(frames, device=0):
+    """Upload a decoded recording ONCE; get_end / signal_noise / load_samples accept the returned CUDA float32
+    tensor in place of the numpy array (classify calls all three on the same frames, src/identify_tracks.py:419-420,
+    502), so the 11.5 MB per minute cross PCIe a single time."""
+    import torch
+    if _is_cuda(frames):
+        return frames
+    return torch.from_numpy(np.ascontiguousarray(frames, dtype=np.float32)).cuda(device)
+
+
 def _finish(block, mean_sub, channels):
     """get_spect tail (src/identify_tracks.py:267,282-287) on [n, n_mels, frames]."""
     block = block[..., None]
@@ -120,8 +134,10 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
                                   "(tf.image.resize_with_pad on a 2-D mfcc with *mel.shape); not built")
     if filter_freqs or filter_below:
         raise NotImplementedError("Butterworth pre-filter is a host pre-step outside this path")
-    # int16 frames (PCM as decoded) are uploaded as they are and widened on the device to sample / 32768
-    frames = np.ascontiguousarray(frames, dtype=np.int16 if getattr(frames, "dtype", None) == np.int16 else np.float32)
+    on_device = _is_cuda(frames)      # to_device(frames): already uploaded, only the results come back
+    if not on_device:
+        # int16 frames (PCM as decoded) are uploaded as they are and widened on the device to sample / 32768
+        frames = np.ascontiguousarray(frames, dtype=np.int16 if getattr(frames, "dtype", None) == np.int16 else np.float32)
     segs, counts = segment_descriptors(len(frames), sr, tracks, segment_length, stride, fmin, fmax,
                                        pad_short_tracks)
     if len(segs) == 0:
@@ -130,7 +146,7 @@ def load_samples(frames, sr, tracks, segment_length, stride, hop_length=281, mea
         fmin, fmax, power, mel_break = 50, 11000, 2, None
     plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break,
                  int(sr * segment_length), int(power), bool(db_scale), bool(normalize))
-    raw = plan.run_host(frames, segs)
+    raw = plan.run(frames, segs).cpu().numpy() if on_device else plan.run_host(frames, segs)
     _check_finite(raw[:, 0, 0])
     block = _finish(raw, mean_sub, channels)
     out, k = [], 0
@@ -209,9 +225,9 @@ def get_end(frames, sr):
     import torch
     from . import engine
     hop_length = 281
-    frames = np.ascontiguousarray(frames, dtype=np.float32)
     plan = _get_end_plan(int(sr))
-    mel, base = plan.run(torch.from_numpy(frames).cuda(plan.device), [0], [frames.shape[0]])
+    dev_frames = to_device(frames, plan.device)
+    mel, base = plan.run(dev_frames, [0], [frames.shape[0]])
     n_frames = int(base[-1])
     chunk_length = sr // hop_length
     mm = engine.chunk_minmax(mel.view(120, n_frames), chunk_length).cpu().numpy()
@@ -239,9 +255,8 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
     the device for the median / morphology stages."""
     import torch
     from . import engine
-    frames = np.ascontiguousarray(frames, dtype=np.float32)
     plan = _signal_noise_plan(int(hop_length))
-    spec, base, a_max = plan.run(torch.from_numpy(frames).cuda(plan.device), [0], [frames.shape[0]], want_max=True)
+    spec, base, a_max = plan.run(to_device(frames, plan.device), [0], [frames.shape[0]], want_max=True)
     engine.scale_by_max(spec, a_max)
     return spec.view(2049, int(base[-1]))
 

@@ -78,3 +78,21 @@ def test_threshold_mask_differs_only_near_thresholds(engine):
 def test_silent_recording_has_no_signals(engine):
     from audio_analysis_b200 import identify_tracks as T
     assert T.signal_noise(np.zeros(48000 * 2, np.float32), 48000) == []
+
+
+def test_frames_uploaded_once_give_the_same_results(engine):
+    """to_device(frames): get_end / signal_noise / load_samples on the CUDA tensor = the calls on the numpy array."""
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(31, seconds=9.0, zero_tail_s=2.0)
+    dev = T.to_device(rec)
+    assert T.get_end(dev, 48000) == T.get_end(rec, 48000)
+    a, b = T.signal_noise(dev, 48000), T.signal_noise(rec, 48000)
+    assert [(s.start, s.end, s.freq_start, s.freq_end) for s in a] == [(s.start, s.end, s.freq_start, s.freq_end) for s in b]
+    kw = dict(hop_length=281, mel_break=1750, n_mels=160, fmin=50, fmax=11000, power=2, db_scale=True, n_fft=4096)
+    tracks = [T.Signal(0.0, 9.0, 0, 24000), T.Signal(1.0, 2.2, 500, 5000)]
+    np.random.seed(2)
+    x = T.load_samples(dev, 48000, tracks, 3.0, 1.5, **kw)
+    np.random.seed(2)
+    y = T.load_samples(rec, 48000, tracks, 3.0, 1.5, **kw)
+    assert [len(t) for t in x] == [len(t) for t in y]
+    assert all(np.array_equal(p, q) for s, t in zip(x, y) for p, q in zip(s, t))
