@@ -90,7 +90,7 @@ struct CiExRead {
 template <int K2>
 struct CiUntangle {
     static __device__ __forceinline__ void run(const double (&zr)[32], const double (&zi)[32], int lane, int partner,
-                                               double t1r, double t1i, double t5r, double t5i, double (&acc)[10]) {
+                                               const double2* lt, double (&acc)[10]) {
         constexpr int pown = out_pos(32, K2);
         constexpr int psend = out_pos(32, 31 - K2);
         constexpr int psend0 = out_pos(32, (32 - K2) & 31);
@@ -101,9 +101,9 @@ struct CiUntangle {
         const double bi = -shfl_d(si, partner);
         const double sumr = ar + br, sumi = ai + bi;
         const double dr = ar - br, di = ai - bi;
-        double ur = t1r, ui = t1i, vr = t5r, vi = t5i;
-        mul_twiddle<K2, 256>(ur, ui);            // W_8192^(32*K2)
-        mul_twiddle<5 * K2, 256>(vr, vi);        // W_8192^(5*32*K2)
+        // u = W_8192^k, v = -i W_8192^(5k) for k = lane + 32 K2, from the host-built table (rows 14 + 2 K2, 15 + 2 K2)
+        const double2 u = lt[(14 + 2 * K2) * 32], v = lt[(15 + 2 * K2) * 32];
+        const double ur = u.x, ui = u.y, vr = v.x, vi = v.y;
         const double gr = fma(vr, dr, fma(-vi, di, fma(ur, sumr, -ui * sumi)));
         const double gi = fma(vr, di, fma(vi, dr, fma(ur, sumi, ui * sumr)));
         const int k = lane + 32 * K2;
@@ -119,7 +119,7 @@ struct CiUntangle {
             acc[8] = fma(m8, m8, acc[8]);
             acc[9] = fma(m9, m9, acc[9]);
         }
-        if constexpr (K2 + 1 < 32) CiUntangle<K2 + 1>::run(zr, zi, lane, partner, t1r, t1i, t5r, t5i, acc);
+        if constexpr (K2 + 1 < 32) CiUntangle<K2 + 1>::run(zr, zi, lane, partner, lt, acc);
     }
 };
 
@@ -154,14 +154,14 @@ __global__ void __launch_bounds__(kCiWarps * 32, 1) ci_bins_kernel(const CiArgs 
     extern __shared__ __align__(16) unsigned char ci_smem_raw[];
     double2* wz = reinterpret_cast<double2*>(ci_smem_raw);          // [512] (w[4m], w[4m+2])
     double2* wz2 = wz + 512;                                         // [512] (w[4m+3], w[4m+1])
-    double2* ltab = wz2 + 512;                                       // [14][32]
-    double2* exall = ltab + 14 * 32;
+    double2* ltab = wz2 + 512;                                       // [kCiLtabRows][32]
+    double2* exall = ltab + kCiLtabRows * 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int m = tid; m < 512; m += kCiWarps * 32) {
         wz[m] = make_double2(a.window[4 * m], a.window[4 * m + 2]);
         wz2[m] = make_double2(a.window[4 * m + 3], a.window[4 * m + 1]);
     }
-    for (int i = tid; i < 14 * 32; i += kCiWarps * 32) ltab[i] = a.ltab[i];
+    for (int i = tid; i < kCiLtabRows * 32; i += kCiWarps * 32) ltab[i] = a.ltab[i];
     __syncthreads();
     double2* ex = exall + warp * kCiExElems;
     const double2* lt = ltab + lane;
@@ -195,8 +195,7 @@ __global__ void __launch_bounds__(kCiWarps * 32, 1) ci_bins_kernel(const CiArgs 
         double acc[10];
 #pragma unroll
         for (int b = 0; b < 10; ++b) acc[b] = 0.0;
-        const double2 t1 = lt[12 * 32], t5 = lt[13 * 32];
-        CiUntangle<0>::run(zr, zi, lane, partner, t1.x, t1.y, t5.x, t5.y, acc);
+        CiUntangle<0>::run(zr, zi, lane, partner, lt, acc);
         double mine = 0.0;
 #pragma unroll
         for (int b = 0; b < 10; ++b) {
@@ -267,7 +266,7 @@ __global__ void __launch_bounds__(256) ci_entries_kernel(const unsigned char* __
     }
 }
 
-size_t ci_smem_bytes() { return sizeof(double2) * (512 + 512 + 14 * 32 + (size_t)kCiWarps * kCiExElems); }
+size_t ci_smem_bytes() { return sizeof(double2) * (512 + 512 + kCiLtabRows * 32 + (size_t)kCiWarps * kCiExElems); }
 
 cudaError_t launch_ci_bins(const CiArgs& a, cudaStream_t st) {
     static bool attr_set[64] = {false};

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 namespace cac {
+constexpr int kCiLtabRows = 14 + 64;   // 14 FFT twiddle rows + (u, v) untangle twiddles for K2 = 0..31
 
 struct CiArgs {
     const float* pcm;
@@ -13,7 +14,7 @@ struct CiArgs {
     int first;                    // window w of a recording starts at item_off + first + hop * w
     int hop;
     const double* window;         // [2048] numpy.hanning(2048)
-    const double2* ltab;          // [14][32] per-lane twiddles (built in cac_ci_plan_create)
+    const double2* ltab;          // [kCiLtabRows][32] per-lane twiddles (built in cac_ci_plan_create)
     double* bins;                 // [n_windows][10]
 };
 

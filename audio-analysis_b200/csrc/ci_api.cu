@@ -12,7 +12,7 @@ using namespace cac;
 struct cac_ci_plan {
     int device;
     double* d_window = nullptr;     // [2048]
-    double2* d_ltab = nullptr;      // [14][32]
+    double2* d_ltab = nullptr;      // [kCiLtabRows][32]
     // item / entry tables staged per call (grown on demand)
     long long* d_tab = nullptr;     size_t tab_cap = 0;
     long long* d_etab = nullptr;    size_t etab_cap = 0;
@@ -43,7 +43,8 @@ extern "C" int cac_ci_plan_create(int32_t window_size, const int32_t* h_edges, c
     CUDA_TRY(cudaSetDevice(device));
     // per-lane twiddles: rows 0-3 W_1024^(8 a lane), rows 4-11 W_1024^(b lane), row 12 W_8192^lane,
     // row 13 -i W_8192^(5 lane)
-    std::vector<double2> lt(14 * 32);
+    // rows 14 + 2 K2 / 15 + 2 K2: W_8192^k and -i W_8192^(5k) for k = lane + 32 K2 (the untangle's twiddles)
+    std::vector<double2> lt(kCiLtabRows * 32);
     const long double tau = 6.283185307179586476925286766559005768L;
     for (int lane = 0; lane < 32; ++lane) {
         for (int a = 0; a < 4; ++a) {
@@ -57,6 +58,12 @@ extern "C" int cac_ci_plan_create(int32_t window_size, const int32_t* h_edges, c
         long double a1 = -tau * (long double)lane / 8192.0L, a5 = -tau * (long double)(5 * lane) / 8192.0L;
         lt[12 * 32 + lane] = make_double2((double)cosl(a1), (double)sinl(a1));
         lt[13 * 32 + lane] = make_double2((double)sinl(a5), (double)-cosl(a5));   // -i (c + i s) = s - i c
+        for (int k2 = 0; k2 < 32; ++k2) {
+            const int k = lane + 32 * k2;
+            const long double b1 = -tau * (long double)k / 8192.0L, b5 = -tau * (long double)((5 * k) % 8192) / 8192.0L;
+            lt[(14 + 2 * k2) * 32 + lane] = make_double2((double)cosl(b1), (double)sinl(b1));
+            lt[(15 + 2 * k2) * 32 + lane] = make_double2((double)sinl(b5), (double)-cosl(b5));
+        }
     }
     cac_ci_plan* plan = new cac_ci_plan();
     plan->device = device;
