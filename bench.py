@@ -62,8 +62,22 @@ def _oracle_one(seed):
     return time.perf_counter() - t0
 
 
+def _one_thread_per_worker():
+    """Pool initializer: one BLAS / OpenMP thread per worker process.  Without it every worker's sgemm
+    (custommel.mel_spec's dense dot) spawns a thread per core and `cores` workers oversubscribe the host so badly
+    that the pool is SLOWER than one process - an unfairly low CPU baseline."""
+    try:
+        from threadpoolctl import threadpool_limits
+        global _TP_LIMIT
+        _TP_LIMIT = threadpool_limits(limits=1)
+    except Exception:
+        for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ[k] = "1"
+
+
 def cpu_oracle_rate(n_recordings, workers):
-    """rec-hours/s of the CPU oracle on `n_recordings` one-minute recordings with `workers` processes."""
+    """rec-hours/s of the CPU oracle on `n_recordings` one-minute recordings with `workers` processes
+    (one compute thread each; a single worker keeps the libraries' default threading, which is how the reference runs)."""
     import multiprocessing as mp
     seeds = [5000 + i for i in range(n_recordings)]
     if workers == 1:
@@ -72,7 +86,7 @@ def cpu_oracle_rate(n_recordings, workers):
             _oracle_one(s)
         wall = time.perf_counter() - t0
     else:
-        with mp.get_context("fork").Pool(workers) as p:
+        with mp.get_context("fork").Pool(workers, initializer=_one_thread_per_worker) as p:
             p.map(_gen, seeds[:workers])          # warm the workers (imports) outside the timing
             t0 = time.perf_counter()
             p.map(_oracle_one, seeds, chunksize=1)
@@ -120,7 +134,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    per_step = max(cores, 8)
+    per_step = max(4 * cores, 8)          # ~15-20 s of CPU work per step with one thread per core
     for _ in range(args.warmup if args.warmup < 1 else 1):
         cpu_oracle_rate(min(cores, per_step), cores)
     rates, walls = [], []
@@ -129,7 +143,8 @@ def run_reference(args, rank, world):
         rates.append(r)
         walls.append(w)
     value = per_step * len(walls) * REC_SECONDS / 3600.0 / sum(walls)
-    sample = "%d one-minute recordings per step (39 segments each), %d worker processes" % (per_step, cores)
+    sample = ("%d one-minute recordings per step (39 segments each), %d worker processes with one BLAS / FFT thread each"
+              % (per_step, cores))
     line = {
         "impl": "reference", "metric": "recording-hours/sec (STFT->mel->dB)", "value": value,
         "unit": "recording-hours/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -346,11 +361,11 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         os.sched_setaffinity(0, all_cpus)                  # the CPU baseline may use every host core again
         cores = os.cpu_count() or 1
-        n = max(cores, 8)
+        n = max(4 * cores, 8)
         v, wall = cpu_oracle_rate(n, cores)
         v1, wall1 = cpu_oracle_rate(2, 1)
         line["cpu_baseline"] = {"value": v, "unit": "recording-hours/s", "cores": cores, "kind": "port",
-                                "sample": "%d one-minute recordings, %d processes, %.1f s wall; single process: %.5f rec-h/s"
+                                "sample": "%d one-minute recordings, %d processes x 1 thread, %.1f s wall; single process with default threading: %.5f rec-h/s"
                                           % (n, cores, wall, v1)}
     print(json.dumps(line), flush=True)
     if world > 1:
