@@ -221,8 +221,8 @@ def _get_end_plan(sr, device=0):
 def get_end(frames, sr):
     """src/identify_tracks.py:387-413: first 1-second chunk of the 120-mel magnitude spectrogram
     (n_fft = sr // 10, hop 281) whose values are all equal (digital silence) -> its start in whole
-    seconds; else the file length.  STFT, mel and the per-chunk min/max run on the GPU."""
-    import torch
+    seconds; else the file length.  STFT, mel and the per-chunk min/max run on the GPU.
+    `frames`: numpy array or the CUDA tensor to_device() returned."""
     from . import engine
     hop_length = 281
     plan = _get_end_plan(int(sr))
