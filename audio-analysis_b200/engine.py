@@ -323,6 +323,14 @@ class CiPlan:
         return out.cpu().numpy()
 
 
+def stft_frame_counts(n_samples, n_fft, hop_length):
+    """Frames librosa.stft(center=True) produces for recordings of n_samples samples (array or scalar):
+    1 + (n + 2 (n_fft // 2) - n_fft) // hop, i.e. 1 + n // hop for even n_fft and 1 + (n - 1) // hop for odd n_fft
+    (0 for an empty recording).  Same rule as cac_spec_frame_count."""
+    ns = np.asarray(n_samples, dtype=np.int64)
+    return np.maximum(0, 1 + (ns + 2 * (int(n_fft) // 2) - int(n_fft)) // int(hop_length))
+
+
 class SpecPlan:
     """Framed-spectrum plan (cac_spec_*): librosa.stft framing -> |X|**power of selected bins,
     optionally through a custommel filterbank."""
@@ -365,8 +373,7 @@ class SpecPlan:
         ns = np.ascontiguousarray(item_samples, dtype=np.int64)
         assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
         assert off.shape == ns.shape and (off + ns <= pcm.numel()).all()
-        n_fft = self.params.n_fft                               # 1 + (n + 2 (n_fft // 2) - n_fft) // hop frames each
-        base = np.concatenate([[0], np.cumsum(np.maximum(0, 1 + (ns + 2 * (n_fft // 2) - n_fft) // self.hop_length))]).astype(np.int64)
+        base = np.concatenate([[0], np.cumsum(stft_frame_counts(ns, self.params.n_fft, self.hop_length))]).astype(np.int64)
         total = int(base[-1])
         if out is None:
             out = torch.empty((total * self.rows,), dtype=torch.float32, device=dev)
