@@ -174,18 +174,24 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
         // real-FFT untangle of the requested bins, H = n_fft / 2:
         //   X[k] = (Z[k] + conj Z[H-k])/2 - (i/2) W_(2H)^k (Z[k] - conj Z[H-k])
         const float2 lc = lt[20 * 32];                                    // cos / sin of 2 pi (kmin + lane) / n_fft
-        float* orow = nullptr;
-        if (!a.n_mels)
-            orow = a.bin_major ? a.out + (size_t)fbase * a.nbins + f : a.out + (size_t)g * a.nbins;
+        // bin k = kmin + lane + 32 r sits at row k % R, column k / R of the Z matrix, its partner H - k likewise: both
+        // (quotient, remainder) pairs are carried from round to round instead of being divided out again, and the
+        // output position walks by a fixed step (bin-major: 32 rows of the recording's [bins][frames] matrix)
+        float* op;
+        size_t ostep = 32;
+        if (a.n_mels) op = pbuf + lane;
+        else if (a.bin_major) { op = a.out + (size_t)fbase * a.nbins + f + (size_t)lane * nfi; ostep = (size_t)32 * nfi; }
+        else op = a.out + (size_t)g * a.nbins + lane;
+        int k = a.kmin + lane;
+        int qa = k / R, ra = k - qa * R;
+        int qb = (kHalf - k) / R, rb = (kHalf - k) - qb * R;
 #pragma unroll 1
-        for (int r = 0; r * 32 < a.nbins; ++r) {
-            const int j = r * 32 + lane;
-            if (j < a.nbins) {
-                const int k = a.kmin + j;
-                const int kk = (k == kHalf) ? 0 : k;
-                const int kp = (k == 0 || k == kHalf) ? 0 : kHalf - k;
-                const float2 za = ex[(kk % R) * kExStride48 + kk / R];
-                const float2 zb = ex[(kp % R) * kExStride48 + kp / R];
+        for (int r = 0; r * 32 < a.nbins; ++r, k += 32, op += ostep) {
+            if (r * 32 + lane < a.nbins) {
+                const int ia = (k == kHalf) ? 0 : ra * kExStride48 + qa;
+                const int ib = (k == 0 || k == kHalf) ? 0 : rb * kExStride48 + qb;
+                const float2 za = ex[ia];
+                const float2 zb = ex[ib];
                 const float2 rc = rtab[r];
                 const float c = fmaf(-rc.y, lc.y, rc.x * lc.x);
                 const float s = fmaf(rc.x, lc.y, rc.y * lc.x);
@@ -199,10 +205,12 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
                 float pw = fmaf(xr, xr, xi * xi);
                 if (a.power == 1) pw = sqrtf(pw);
                 vmax = fmaxf(vmax, pw);
-                if (a.n_mels) pbuf[j] = pw;
-                else if (a.bin_major) orow[(size_t)j * nfi] = pw;
-                else orow[j] = pw;
+                *op = pw;
             }
+            ra += 32 % R; qa += 32 / R;
+            if (ra >= R) { ra -= R; ++qa; }
+            rb -= 32 % R; qb -= 32 / R;
+            if (rb < 0) { rb += R; --qb; }
         }
         if (a.n_mels) {
             for (int i = a.nbins + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;
