@@ -28,33 +28,31 @@ void keep_pool_warm() {
 }
 }  // namespace
 
-extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
-                                     int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
-                                     uint8_t* d_stage_masks, void* stream) {
-    if (!d_spec || !h_stats || !h_count) return fail(CAC_ERR_INVALID, "null argument");
+// Launches the whole chain on `st`; the result block d_small = [count, -, -, -, 6 ints per component ...] stays on the
+// device (d_small == nullptr: allocated here and returned through *d_small_out, owned by the Scratch).
+static int components_launch(Scratch& s, const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                             int32_t erode_h, int32_t max_components, uint8_t* d_stage_masks, int* d_small,
+                             int** d_small_out, cudaStream_t st) {
     if (rows < 1 || cols < 1 || (int64_t)rows * cols > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "matrix size out of range");
     if (dilate_h < 1 || dilate_w < 1 || erode_h < 1 || dilate_h > 255 || dilate_w > 4096 || max_components < 1)
         return fail(CAC_ERR_INVALID, "kernel size / max_components out of range");
-    cudaStream_t st = (cudaStream_t)stream;
     const size_t n = (size_t)rows * cols;
-    keep_pool_warm();
-    Scratch s(st);
     float *d_t, *d_med;
-    int* d_small;
     const size_t wpr = (size_t)((cols + 31) / 32), nw = (size_t)rows * wpr;
     // d_t doubles as the label array later (same size: 4 bytes per cell)
     CUDA_TRY(cudaMallocAsync(&s.p[0], n * sizeof(float), st));
     CUDA_TRY(cudaMallocAsync(&s.p[1], n * sizeof(int), st));
     CUDA_TRY(cudaMallocAsync(&s.p[2], 3 * nw * sizeof(unsigned), st));
     CUDA_TRY(cudaMallocAsync(&s.p[3], ((size_t)rows + cols) * sizeof(float), st));
-    CUDA_TRY(cudaMallocAsync(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int), st));
+    if (!d_small) CUDA_TRY(cudaMallocAsync(&s.p[4], ((size_t)max_components * 6 + 4) * sizeof(int), st));
     d_t = (float*)s.p[0];
     int* d_rootid = (int*)s.p[1];
     unsigned* m0 = (unsigned*)s.p[2];              // bit-packed masks (track_bits.cu): 2.6 MB each for a one-minute recording
     unsigned* m1 = m0 + nw;
     unsigned* m2 = m1 + nw;
     d_med = (float*)s.p[3];
-    d_small = (int*)s.p[4];
+    if (!d_small) d_small = (int*)s.p[4];
+    if (d_small_out) *d_small_out = d_small;
     float* rowmed = d_med;
     float* colmed = d_med + rows;
 
@@ -75,6 +73,21 @@ extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t 
     // cv2.connectedComponentsWithStats (8-connectivity) (:686), on horizontal runs
     int* d_stats = d_small + 4;
     CUDA_TRY(launch_ccl_runs(m0, (int*)d_t, d_rootid, rows, (int)cols, d_small, d_stats, max_components, st));
+    return CAC_OK;
+}
+
+extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                                     int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
+                                     uint8_t* d_stage_masks, void* stream) {
+    if (!d_spec || !h_stats || !h_count) return fail(CAC_ERR_INVALID, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_warm();
+    Scratch s(st);
+    int* d_small = nullptr;
+    int rc = components_launch(s, d_spec, rows, cols, dilate_h, dilate_w, erode_h, max_components, d_stage_masks, nullptr,
+                               &d_small, st);
+    if (rc) return rc;
+    int* d_stats = d_small + 4;
     int count = 0;
     CUDA_TRY(cudaMemcpyAsync(&count, d_small, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
@@ -88,4 +101,17 @@ extern "C" int cac_signal_components(const float* d_spec, int32_t rows, int64_t 
     }
     *h_count = count;
     return CAC_OK;
+}
+
+// The same chain without the read-back: everything is queued on `stream` and the result block stays on the device
+// (d_result: 4 + 6 * max_components ints - [0] = number of components, then per component
+// {min x, min y, max x, max y, area, order}).  For batches: queue one call per recording, synchronise once.
+extern "C" int cac_signal_components_async(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h,
+                                           int32_t dilate_w, int32_t erode_h, int32_t max_components, int32_t* d_result,
+                                           void* stream) {
+    if (!d_spec || !d_result) return fail(CAC_ERR_INVALID, "null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    keep_pool_warm();
+    Scratch s(st);          // freed in stream order when the call returns: safe, later work on `st` comes after it
+    return components_launch(s, d_spec, rows, cols, dilate_h, dilate_w, erode_h, max_components, nullptr, d_result, nullptr, st);
 }

@@ -78,6 +78,7 @@ lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
 lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
 lib.cac_signal_components.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]
+lib.cac_signal_components_async.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp]
 lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
@@ -88,7 +89,7 @@ lib.cac_resample_out_len.argtypes = [_vp, _i64]
 lib.cac_resample_out_len.restype = _i64
 lib.cac_resample_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 
-EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_signal_components", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_signal_components", "cac_signal_components_async", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
@@ -524,6 +525,32 @@ class pinned:
     def __exit__(self, *exc):
         lib.cac_host_unregister(self.arr.ctypes.data_as(_vp))
         return False
+
+
+def signal_components_queue(spec, dilate_h, dilate_w, erode_h, result):
+    """cac_signal_components_async: queue the chain for one recording; `result` is a CUDA int32 tensor of
+    4 + 6 * max_components values that receives [count, -, -, -, (min x, min y, max x, max y, area, order) ...]."""
+    torch = _torch()
+    assert spec.is_cuda and spec.dtype == torch.float32 and spec.is_contiguous() and spec.dim() == 2
+    assert result.is_cuda and result.dtype == torch.int32 and result.is_contiguous()
+    rows, cols = spec.shape
+    max_components = (result.numel() - 4) // 6
+    with torch.cuda.device(spec.device):
+        check(lib.cac_signal_components_async(spec.data_ptr(), rows, cols, int(dilate_h), int(dilate_w), int(erode_h),
+                                              int(max_components), result.data_ptr(), _stream_ptr(torch)))
+
+
+def signal_components_collect(result_host):
+    """[count, ...] block (numpy int32, downloaded) -> [n, 6] = (x, y, width, height, area, order)."""
+    count = int(result_host[0])
+    max_components = (result_host.size - 4) // 6
+    if count > max_components:
+        raise CacError("more connected components than max_components")
+    raw = result_host[4:4 + 6 * count].reshape(count, 6)
+    out = raw.copy()
+    out[:, 2] = raw[:, 2] - raw[:, 0] + 1
+    out[:, 3] = raw[:, 3] - raw[:, 1] + 1
+    return out
 
 
 def signal_components(spec, dilate_h, dilate_w, erode_h, max_components=65536, want_masks=False):

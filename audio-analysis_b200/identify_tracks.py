@@ -264,6 +264,51 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
 SIGNAL_WIDTH = 0.25   # src/identify_tracks.py:21
 
 
+def _signals_from_stats(stats, sr, width, height, freqs, signal_cls):
+    """Reference filter (:689-691) and time / frequency conversion (:697-704, with its hard-coded 281) of the
+    component table [n, 6] = (x, y, w, h, area, order)."""
+    stats = stats[np.argsort(stats[:, 5], kind="stable")]         # cv2's label order ...
+    stats = stats[np.argsort(stats[:, 0], kind="stable")]         # ... then sorted(stats, key=x) (stable)
+    min_width = 0.65 * width
+    min_height = height - height // 10
+    signals = []
+    for x, y, w, h, _, _ in stats.tolist():
+        if not (w > min_width and h > min_height):
+            continue
+        max_freq = min(len(freqs) - 1, y + h)
+        signals.append((signal_cls or Signal)(x * 281 / sr, (x + w) * 281 / sr, freqs[y], freqs[max_freq]))
+    return signals
+
+
+def signal_noise_batch(recordings, sr, hop_length=281, signal_cls=None, max_components=4096):
+    """signal_noise (src/identify_tracks.py:650-706) for MANY recordings with one synchronisation: `recordings` is a list
+    of 1-D numpy arrays / CUDA tensors or a 2-D array / tensor [n, samples].  Per recording the spectrum, its maximum,
+    the scaling and the median / mask / morphology / component chain (cac_signal_components_async) are queued on the
+    current stream; the small component tables come back together at the end.  Returns one list of Signal per
+    recording, equal to signal_noise() called on each."""
+    import torch
+    from . import engine
+    n_fft = 4096
+    plan = _signal_noise_plan(int(hop_length))
+    width = int(SIGNAL_WIDTH * sr / hop_length)
+    freqs = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
+    above = np.nonzero(freqs > 100)[0]
+    height = int(above[0]) + 1 if len(above) else 0
+    items = [recordings[i] for i in range(len(recordings))]
+    if not items:
+        return []
+    dev = torch.device("cuda", plan.device)
+    results = torch.empty((len(items), 4 + 6 * max_components), dtype=torch.int32, device=dev)
+    for i, rec in enumerate(items):
+        frames = to_device(rec, plan.device)
+        spec, base, a_max = plan.run(frames, [0], [frames.shape[0]], want_max=True)
+        engine.scale_by_max(spec, a_max)
+        engine.signal_components_queue(spec.view(2049, int(base[-1])), height, width, height // 10, results[i])
+    host = results.cpu().numpy()                                  # the one synchronisation
+    return [_signals_from_stats(engine.signal_components_collect(host[i]), sr, width, height, freqs, signal_cls)
+            for i in range(len(items))]
+
+
 def signal_noise(frames, sr, hop_length=281, signal_cls=None):
     """src/identify_tracks.py:650-706: candidate track signals of a recording (`signal_cls`: the class to
     build, e.g. the reference's own Signal with its merge helpers; default: this module's Signal).  STFT magnitude,
@@ -279,14 +324,4 @@ def signal_noise(frames, sr, hop_length=281, signal_cls=None):
     above = np.nonzero(freqs > 100)[0]
     height = int(above[0]) + 1 if len(above) else 0
     stats = engine.signal_components(spec, height, width, height // 10)
-    stats = stats[np.argsort(stats[:, 5], kind="stable")]         # cv2's label order ...
-    stats = stats[np.argsort(stats[:, 0], kind="stable")]         # ... then sorted(stats, key=x) (stable)
-    min_width = 0.65 * width
-    min_height = height - height // 10
-    signals = []
-    for x, y, w, h, _, _ in stats.tolist():
-        if not (w > min_width and h > min_height):
-            continue
-        max_freq = min(len(freqs) - 1, y + h)
-        signals.append((signal_cls or Signal)(x * 281 / sr, (x + w) * 281 / sr, freqs[y], freqs[max_freq]))
-    return signals
+    return _signals_from_stats(stats, sr, width, height, freqs, signal_cls)

@@ -206,6 +206,13 @@ int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32
                           int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
                           uint8_t* d_stage_masks, void* stream);
 
+/* The same chain queued on `stream` without the read-back, for batches (one call per recording, one synchronisation
+ * for all): d_result receives 4 + 6 * max_components int32 - [0] = number of components (the call's results are
+ * invalid if it exceeds max_components), then from [4] per component {min x, min y, max x, max y, area, order}
+ * (width = max x - min x + 1, height likewise).  Scratch is allocated and freed in stream order. */
+int cac_signal_components_async(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                                int32_t erode_h, int32_t max_components, int32_t* d_result, void* stream);
+
 /* Rational-rate resampling front-end: replaces `ffmpeg -ar 16000` in front of the Cacophony
  * Index (src/common.py:76-79) and librosa.resample to 48 kHz (src/identify_tracks.py:55-57).  The filter is the
  * caller's: `h_taps` is the zero-padded polyphase prototype and `n_pre_remove` the number of leading outputs to

@@ -96,3 +96,24 @@ def test_frames_uploaded_once_give_the_same_results(engine):
     y = T.load_samples(rec, 48000, tracks, 3.0, 1.5, **kw)
     assert [len(t) for t in x] == [len(t) for t in y]
     assert all(np.array_equal(p, q) for s, t in zip(x, y) for p, q in zip(s, t))
+
+
+def test_signal_noise_batch_equals_per_recording_calls(engine):
+    """signal_noise_batch queues every recording's chain (cac_signal_components_async) and synchronises once."""
+    import time
+    import torch
+    from audio_analysis_b200 import identify_tracks as T
+    recs = [synth.recording(70 + i, seconds=s) for i, s in enumerate((8.0, 11.5, 6.0))]
+    key = lambda sigs: [(s.start, s.end, s.freq_start, s.freq_end) for s in sigs]
+    single = [key(T.signal_noise(r, 48000)) for r in recs]
+    batch = T.signal_noise_batch(recs, 48000)
+    assert [key(b) for b in batch] == single
+    assert T.signal_noise_batch([], 48000) == []
+    # throughput note (printed with -s): 16 one-minute recordings already on the device
+    pool = torch.from_numpy(synth.batch(500, 16, seconds=60.0)).cuda()
+    T.signal_noise_batch(pool[:2], 48000)
+    t0 = time.perf_counter()
+    out = T.signal_noise_batch(pool, 48000)
+    dt = time.perf_counter() - t0
+    print("signal_noise_batch: %.3f ms per one-minute recording (16 per call)" % (dt / 16 * 1e3))
+    assert len(out) == 16 and key(out[3]) == key(T.signal_noise(pool[3], 48000))
