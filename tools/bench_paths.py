@@ -112,8 +112,31 @@ def bench_hop281(n_rec=64):
         del out
 
 
+def bench_signal_noise_batch(n_rec=32):
+    """Track finding (signal_noise, src/identify_tracks.py:650-706) for a batch of one-minute recordings that are
+    already on the device: spectrum, scaling, medians, bit-packed morphology, run-based components, one
+    synchronisation for all component tables (identify_tracks.signal_noise_batch); wall clock."""
+    from audio_analysis_b200 import identify_tracks as T
+    pool = np.stack([synth.recording(700 + i, 60.0, 48000) for i in range(16)])
+    pcm = torch.from_numpy(pool).cuda().repeat((n_rec + 15) // 16, 1)[:n_rec].contiguous()
+    T.signal_noise_batch(pcm[:2], 48000)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = T.signal_noise_batch(pcm, 48000)
+    wall = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    for i in range(4):
+        T.signal_noise(pcm[i], 48000)
+    single = (time.perf_counter() - t0) / 4
+    print(json.dumps({"path": "signal_noise_batch", "recordings": n_rec, "ms_per_recording": wall / n_rec * 1e3,
+                      "ms_per_recording_single_calls": single * 1e3, "recording_hours_per_s": n_rec / 60.0 / wall,
+                      "signals_first_recording": len(out[0]), "dtype": "f32"}), flush=True)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["ci"]
+    if "signal_noise" in which:
+        bench_signal_noise_batch()
     if "hop281" in which:
         bench_hop281()
     if "ci" in which:
