@@ -3,6 +3,7 @@
 // every compute entry point fails with CAC_ERR_NO_DEVICE / CAC_ERR_CUDA.
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -61,6 +62,9 @@ struct cac_plan {
     cac_segment* d_segs = nullptr; size_t segs_cap = 0;
     float* d_out = nullptr;      size_t out_cap = 0;
     void* d_work = nullptr;      size_t work_cap = 0;
+    // MagTransform epilogue (cac_plan_set_magtransform)
+    int mag_on = 0;
+    float mag_a = 0.f;
     // optional CUDA events bracketing the dominant (stft_mel) kernel of the last cac_features_run
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // cac_features_host pipeline: upload / compute / download streams and per-chunk events
@@ -117,8 +121,7 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     plan->frames_per_stage = 0;
     static const int kFsChoices[] = {24, 12, 10, 8, 6, 4, 3, 2, 1};
     for (int fs : kFsChoices) {
-        int stage_len = (fs - 1) * p.hop_length + 4096;
-        int half = (((stage_len + 8 + 1) / 2 + 1 + 31) / 32) * 32 + 16;   // also sizes the raw buffer (stage_len + 8)
+        int half = stage_half_floats(fs, p.hop_length);
         FeatArgs a{};
         a.stage_half = half;
         a.nbins = kmax - kmin + 1;
@@ -230,6 +233,17 @@ extern "C" int cac_plan_last_kernel_ms(cac_plan* plan, float* ms) {
     return CAC_OK;
 }
 
+extern "C" int cac_plan_set_magtransform(cac_plan* plan, int enable, float a) {
+    if (!plan) return fail(CAC_ERR_INVALID, "null plan");
+    if (enable && plan->p.db_scale)
+        return fail(CAC_ERR_INVALID, "MagTransform replaces the dB scale: the plan must be created with db_scale = 0");
+    if (enable && (!plan->fused_unsupported.empty()))
+        return fail(CAC_ERR_INVALID, "the MagTransform epilogue exists in the fused n_fft 4096 kernel only; use cac_magtransform_run");
+    plan->mag_on = enable ? 1 : 0;
+    plan->mag_a = a;
+    return CAC_OK;
+}
+
 extern "C" int cac_plan_frames(const cac_plan* plan) { return plan ? plan->n_frames : CAC_ERR_INVALID; }
 
 static size_t align128(size_t v) { return (v + 127) / 128 * 128; }
@@ -317,6 +331,8 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     for (int g = 0; g < 16; ++g) { a.gmax[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
     a.stage_half = plan->stage_half;
     a.normalize = plan->p.normalize;
+    a.mag_on = plan->mag_on;
+    a.mag_p = 1.0f / (1.0f + expf(-plan->mag_a));            // tf.math.sigmoid in float32
     CUDA_TRY(launch_features(a, plan->p.power, plan->p.db_scale, st, plan->ev0, plan->ev1));
     return CAC_OK;
 }

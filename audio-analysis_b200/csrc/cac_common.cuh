@@ -45,7 +45,18 @@ struct FeatArgs {
     int goff[16];          // offset of group g inside wpad
     int stage_half;        // floats reserved for each of the even/odd sample planes
     int normalize;
+    // MagTransform fused into the flush (src/magtransform.py:17-19, src/magtransformv2.py:19-21): when mag_on the
+    // value leaving the kernel is mel ** mag_p, mag_p = sigmoid(a) (only without db_scale; cac_plan_set_magtransform)
+    int mag_on;
+    float mag_p;
 };
+
+// floats reserved for each of the even / odd sample planes of a stage of `frames` consecutive 4096-sample frames
+// (stft_mel.cu, sn_stft.cu)
+__host__ __device__ inline int stage_half_floats(int frames, int hop) {
+    const int stage_len = (frames - 1) * hop + 4096;
+    return (((stage_len + 8 + 1) / 2 + 1 + 31) / 32) * 32 + 16;
+}
 
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll

@@ -1,0 +1,204 @@
+// signal_noise's spectrum for a wave of recordings (src/identify_tracks.py:652-659):
+//   spectogram = np.abs(librosa.stft(frames, n_fft=4096, hop_length=hop))      -> spec [2049][cols], unscaled
+//   a_max = np.amax(spectogram)                                                -> amax (float bits, atomicMax)
+//   column_medians = np.median(spectogram / a_max, axis=0)                     -> colmed [cols], unscaled
+// Division by a_max is monotone, so the order statistic is selected on the unscaled magnitudes here and scaled
+// where it is consumed (sn_rows.cu) - bit-identical to dividing first, and a_max is not known before this kernel ends.
+//
+// Same structure as stft_mel_kernel: persistent, one CTA of 12 warps per SM, work unit = a stage of
+// frames_per_stage consecutive frames of one recording, samples of stage q + 1 arrive by cp.async while stage q is
+// transformed, one warp per frame (fft4096.cuh).  The warp that transformed a frame still holds its 2,049
+// magnitudes: it stores them bin-major (one float per row of the recording's matrix; the 12 warps of the CTA
+// work on consecutive frames, L2 merges the sectors), and selects their median by a four-pass radix select whose
+// histogram reuses the warp's exchange buffer - no transpose, no second matrix, no extra pass over HBM.
+#include "cac_common.cuh"
+#include "fft4096.cuh"
+#include "sn.cuh"
+#include "sn_select.cuh"
+
+namespace cac {
+
+struct SnStftSmem { int raw, stage, ex, ltab, total; };   // offsets in floats
+__host__ __device__ inline SnStftSmem sn_stft_layout(int stage_half) {
+    SnStftSmem L;
+    int o = 0;
+    L.raw = o; o += 2 * stage_half;
+    L.stage = o; o += 2 * stage_half;
+    L.ex = o; o += kWarpsPerCta * kExFloats;
+    L.ltab = o; o += 32 * 32;
+    L.total = o;
+    return L;
+}
+
+// median (rank 1024 of the 2,049 magnitudes of one frame): lane holds bins lane + 32 i in v[], lane 0 also bin 2048
+__device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], float nyq, unsigned* hist, int lane) {
+    unsigned prefix = 0u, k = 1024u;
+    uint4* h4 = reinterpret_cast<uint4*>(hist);
+    unsigned* hl = hist + (lane & 3);
+    const unsigned ekey = __float_as_uint(nyq);
+#pragma unroll 1
+    for (int pass = 3; pass >= 0; --pass) {
+        const int shift = 8 * pass;
+        const unsigned himask = pass == 3 ? 0u : (0xffffffffu << (shift + 8));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) h4[lane + 32 * j] = make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+            const unsigned key = __float_as_uint(v[i]);
+            if ((key & himask) == prefix) atomicAdd(hl + ((key >> shift) & 255u) * 4, 1u);
+        }
+        if (lane == 0 && (ekey & himask) == prefix) atomicAdd(hl + ((ekey >> shift) & 255u) * 4, 1u);
+        __syncwarp();
+        const unsigned digit = sel_scan_digit(hist, lane, k);
+        prefix |= digit << shift;
+        __syncwarp();                                   // every lane has read the histogram before it is cleared again
+    }
+    return prefix;
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const float* __restrict__ pcm, const SnWave w,
+                                                                       int hop, int fps, int stage_half) {
+    extern __shared__ __align__(16) float smem[];
+    const SnStftSmem L = sn_stft_layout(stage_half);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* ex = smem + L.ex + warp * kExFloats;
+    float* pbuf = ex;                                    // magnitudes reuse the exchange buffer (fft_frame), then the histogram does
+    unsigned* hist = reinterpret_cast<unsigned*>(ex);
+    float* ltab = smem + L.ltab;
+    if (warp == 0) init_lane_table(ltab, lane);
+    const float* lt = ltab + lane;
+
+    const SnItem last = w.items[w.n_items - 1];
+    const long long n_stages = last.stage_base + last.n_stages;
+    const long long q_begin = n_stages * blockIdx.x / gridDim.x, q_end = n_stages * (blockIdx.x + 1) / gridDim.x;
+    const int n_my = (int)(q_end - q_begin);
+    if (n_my <= 0) return;
+    int item = 0;
+    while (w.items[item].stage_base + w.items[item].n_stages <= q_begin) ++item;
+    int sidx = (int)(q_begin - w.items[item].stage_base);
+
+    auto plane_buf = [&](int parity) { return smem + (parity ? L.stage : L.raw); };
+    // staged element u of stage (item, sidx) = sample f0 * hop - 2048 + u of the recording, zero outside it
+    // (librosa's centre padding); thread t owns u = t, t + 384, ...: fixed plane (384 is even)
+    auto issue_stage = [&](int it_idx, int s, int parity) {
+        const SnItem im = w.items[it_idx];
+        const int f0 = s * fps;
+        const int nfs = min(fps, im.cols - f0);
+        const int len = (nfs - 1) * hop + kNfft;
+        const float* src = pcm + im.pcm_off;
+        const int r0 = f0 * hop - kNfft / 2;
+        constexpr int kT = kWarpsPerCta * 32;
+        float* dst = plane_buf(parity) + (tid & 1) * stage_half + (tid >> 1);
+        const int n_steps = (len - tid + kT - 1) / kT;
+        const int first = r0 + tid;
+        int k_lo = first >= 0 ? 0 : (-first + kT - 1) / kT;
+        int k_hi = im.n_samples > first ? (im.n_samples - first + kT - 1) / kT : 0;
+        k_lo = min(k_lo, n_steps);
+        k_hi = max(k_lo, min(k_hi, n_steps));
+        for (int k = 0; k < k_lo; ++k) dst[k * (kT / 2)] = 0.f;
+        const float* g = src + first + (long long)k_lo * kT;
+        float* d = dst + k_lo * (kT / 2);
+#pragma unroll 4
+        for (int k = k_lo; k < k_hi; ++k, g += kT, d += kT / 2) cp_async4(d, g, true);
+        for (int k = k_hi; k < n_steps; ++k) dst[k * (kT / 2)] = 0.f;
+        cp_async_commit();
+    };
+
+    issue_stage(item, sidx, 0);
+    for (int it = 0; it < n_my; ++it) {
+        const SnItem im = w.items[item];
+        const int f0 = sidx * fps;
+        const int nfs = min(fps, im.cols - f0);
+        float* se = plane_buf(it & 1);
+        float* so = se + stage_half;
+        const bool last_of_item = sidx + 1 == im.n_stages;
+
+        cp_async_wait_all();
+        __syncthreads();                       // stage `it` has landed; every warp is done with stage it - 1
+        if (it + 1 < n_my) issue_stage(last_of_item ? item + 1 : item, last_of_item ? 0 : sidx + 1, (it + 1) & 1);
+
+        float* spec = w.spec + (size_t)item * w.spec_stride;
+        float* colmed = w.colmed + (size_t)item * w.col_stride;
+        const size_t rstep = (size_t)32 * im.cols;
+        float vmax = 0.f;
+#pragma unroll 1
+        for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
+            fft_frame<1, 32, true>(se, so, fi * hop, ex, pbuf, lane, lt);
+            __syncwarp();                      // lane 0's bin 2048 is visible
+            float v[64];
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = pbuf[lane + 32 * i];     // the lane's own values, 2 |X[k]|
+            const float nyq = pbuf[2048];
+            __syncwarp();                      // the buffer is free: it becomes the histogram
+            float m = nyq;
+#pragma unroll
+            for (int i = 0; i < 64; ++i) m = fmaxf(m, v[i]);
+            vmax = fmaxf(vmax, m);
+            const int f = f0 + fi;
+            float* o = spec + (size_t)lane * im.cols + f;
+#pragma unroll
+            for (int i = 0; i < 64; ++i, o += rstep) *o = 0.5f * v[i];
+            if (lane == 0) spec[(size_t)2048 * im.cols + f] = 0.5f * nyq;
+            const unsigned med = frame_median_bits(v, nyq, hist, lane);
+            if (lane == 0) colmed[f] = 0.5f * __uint_as_float(med);
+        }
+        vmax = warp_max(vmax);
+        if (lane == 0) atomicMax(w.amax + item, __float_as_uint(0.5f * vmax));
+        if (last_of_item) { ++item; sidx = 0; } else ++sidx;
+    }
+}
+
+// item table of a wave (one thread: a wave holds at most a few dozen recordings)
+__global__ void sn_prep_kernel(const long long* __restrict__ off, const long long* __restrict__ len, int n, int hop, int fps,
+                               long long max_len, SnItem* __restrict__ items, unsigned* __restrict__ amax) {
+    if (threadIdx.x == 0) {
+        int base = 0;
+        for (int i = 0; i < n; ++i) {
+            SnItem im;
+            im.pcm_off = off[i];
+            im.n_samples = (int)max(0LL, min(len[i], max_len));   // never beyond the slot the caller sized
+            im.cols = 1 + im.n_samples / hop;
+            im.wpr = (im.cols + 31) / 32;
+            im.stage_base = base;
+            im.n_stages = (im.cols + fps - 1) / fps;
+            im.pad = 0;
+            base += im.n_stages;
+            items[i] = im;
+        }
+    }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) amax[i] = 0u;
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+size_t sn_stft_smem_bytes(int frames_per_stage, int hop) {
+    return sizeof(float) * (size_t)sn_stft_layout(stage_half_floats(frames_per_stage, hop)).total;
+}
+
+int sn_stft_frames_per_stage(int hop) {
+    static const int kChoices[] = {24, 12, 10, 8, 6, 4, 3, 2, 1};
+    for (int fs : kChoices)
+        if (sn_stft_smem_bytes(fs, hop) <= 227 * 1024) return fs;
+    return 0;
+}
+
+cudaError_t launch_sn_prep(const long long* d_item_off, const long long* d_item_len, int n_items, int hop,
+                           int frames_per_stage, long long max_item_samples, SnItem* items, unsigned* amax, cudaStream_t st) {
+    sn_prep_kernel<<<1, 64, 0, st>>>(d_item_off, d_item_len, n_items, hop, frames_per_stage, max_item_samples, items, amax);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sn_stft(const float* pcm, const SnWave& w, int hop, int frames_per_stage, cudaStream_t st) {
+    const size_t smem = sn_stft_smem_bytes(frames_per_stage, hop);
+    cudaError_t e = cudaFuncSetAttribute(sn_stft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // persistent: one CTA per SM; the stage count lives on the device, CTAs without stages leave at once
+    sn_stft_kernel<<<(unsigned)sms, kWarpsPerCta * 32, smem, st>>>(pcm, w, hop, frames_per_stage,
+                                                                   stage_half_floats(frames_per_stage, hop));
+    return cudaGetLastError();
+}
+
+}  // namespace cac

@@ -12,7 +12,7 @@ struct SpecArgs {
     const long long* item_len;     // [n_items] samples per recording
     const long long* frame_base;   // [n_items + 1] prefix sum of frames
     int n_items;
-    long long n_frames_total;
+    long long n_frames_total;      // < 0: read frame_base[n_items] on the device (tables built by a prep kernel)
     int n_fft;                     // see spec4800_supported()
     int hop;
     int power;                     // 1: |X|, 2: |X|^2
@@ -22,6 +22,10 @@ struct SpecArgs {
     int bin_major;                 // raw output layout: 0 = [frame][bin] (global frames), 1 = per item [bin][frame]
     float* out;
     float* gmax;                   // optional: atomicMax target (float bits as unsigned), may be NULL
+    // get_end's chunk scan fused into the mel epilogue (src/identify_tracks.py:404-412): when chunk_mm is set the mel
+    // values are not stored; chunk_mm[item * chunk_stride + frame / chunk_frames] = {min, max} (float bits, values >= 0)
+    uint2* chunk_mm;
+    int chunk_frames, chunk_stride;
     // per-plan tables
     const float2* ltab;            // per-lane twiddle / window constants
     const float2* rtab;            // per-round untangle twiddles
@@ -45,5 +49,11 @@ cudaError_t launch_chunk_minmax(const float* in, int n_rows, long long n_cols, i
 cudaError_t launch_morepork_windows(const float* spec, const long long* win_frame0, const int* win_width,
                                     long long n_windows, int n_bins, float* out, cudaStream_t st);
 cudaError_t launch_scale_by_max(float* data, long long n, const float* gmax, cudaStream_t st);
+// get_end for a batch (device item tables): tab = [item_off | item_len | frame_base] (3 n + 1), mm = per-chunk {min, max}
+cudaError_t launch_get_end_prep(const long long* d_item_off, const long long* d_item_len, int n_items, int n_fft, int hop,
+                                long long max_item_samples, long long* tab, uint2* mm, int chunk_stride, int* out,
+                                cudaStream_t st);
+cudaError_t launch_get_end_scan(const long long* tab, int n_items, const uint2* mm, int chunk_stride, int chunk_frames,
+                                int* out, cudaStream_t st);
 
 }  // namespace cac

@@ -224,3 +224,74 @@ extern "C" int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec
     CUDA_TRY(launch_morepork_windows(d_spec, plan->d_wtab, d_width, n_windows, plan->nbins, d_out, st));
     return CAC_OK;
 }
+
+// ---- identify_tracks.get_end for a batch (device item tables, chunk scan on the device) -----------------------------
+namespace {
+struct GetEndLayout { size_t tab, mm, total; int chunk_stride; };
+GetEndLayout get_end_layout(const cac_spec_plan* plan, int64_t n_items, int64_t max_item_samples, int chunk_frames) {
+    GetEndLayout L;
+    const long long max_frames = frames_of(plan, max_item_samples);
+    L.chunk_stride = (int)(max_frames / chunk_frames + 1);
+    size_t o = 0;
+    L.tab = o; o += ((3 * (size_t)n_items + 1) * sizeof(long long) + 255) / 256 * 256;
+    L.mm = o; o += ((size_t)n_items * L.chunk_stride * sizeof(uint2) + 255) / 256 * 256;
+    L.total = o;
+    return L;
+}
+}  // namespace
+
+extern "C" size_t cac_get_end_work_bytes(const cac_spec_plan* plan, int64_t n_items, int64_t max_item_samples,
+                                         int32_t chunk_frames) {
+    if (!plan || n_items < 1 || max_item_samples < 0 || chunk_frames < 1) return 0;
+    return get_end_layout(plan, n_items, max_item_samples, chunk_frames).total;
+}
+
+extern "C" int cac_get_end_run(cac_spec_plan* plan, const float* d_pcm, const int64_t* d_item_offset,
+                               const int64_t* d_item_samples, int64_t n_items, int64_t max_item_samples, int32_t chunk_frames,
+                               int32_t* d_out, void* d_work, size_t work_bytes, void* stream) {
+    if (!plan || !d_pcm || !d_item_offset || !d_item_samples || !d_out || !d_work) return fail(CAC_ERR_INVALID, "null argument");
+    if (plan->p.n_mels < 1 || plan->dft) return fail(CAC_ERR_INVALID, "get_end needs a mel plan of the mixed-radix kernel");
+    if (n_items < 0 || n_items > 0x7fffffffLL || max_item_samples < 0 || chunk_frames < 1)
+        return fail(CAC_ERR_INVALID, "n_items / max_item_samples / chunk_frames out of range");
+    if (n_items == 0) return CAC_OK;
+    const GetEndLayout L = get_end_layout(plan, n_items, max_item_samples, chunk_frames);
+    if (work_bytes < L.total || ((uintptr_t)d_work & 255) != 0)
+        return fail(CAC_ERR_INVALID, "work buffer too small or not 256-byte aligned (see cac_get_end_work_bytes)");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(plan->device));
+    long long* tab = reinterpret_cast<long long*>((char*)d_work + L.tab);
+    uint2* mm = reinterpret_cast<uint2*>((char*)d_work + L.mm);
+    CUDA_TRY(launch_get_end_prep(reinterpret_cast<const long long*>(d_item_offset),
+                                 reinterpret_cast<const long long*>(d_item_samples), (int)n_items, plan->p.n_fft,
+                                 plan->p.hop_length, max_item_samples, tab, mm, L.chunk_stride, d_out, st));
+    SpecArgs a{};
+    a.pcm = d_pcm;
+    a.item_off = tab;
+    a.item_len = tab + n_items;
+    a.frame_base = tab + 2 * n_items;
+    a.n_items = (int)n_items;
+    a.n_frames_total = -1;                    // on the device: tab[3 n]
+    a.n_fft = plan->p.n_fft;
+    a.hop = plan->p.hop_length;
+    a.power = plan->p.power;
+    a.kmin = plan->kmin;
+    a.nbins = plan->nbins;
+    a.n_mels = plan->p.n_mels;
+    a.bin_major = 0;
+    a.out = nullptr;                          // the mel values are consumed in the epilogue
+    a.gmax = nullptr;
+    a.chunk_mm = mm;
+    a.chunk_frames = chunk_frames;
+    a.chunk_stride = L.chunk_stride;
+    a.ltab = plan->d_ltab;
+    a.rtab = plan->d_rtab;
+    a.wpad = plan->d_wpad;
+    a.mstart = plan->d_mstart;
+    a.n_taps = (int)plan->mb.wpad.size();
+    a.n_groups = plan->mb.n_groups;
+    a.pbuf_len = plan->mb.pbuf_len;
+    for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
+    CUDA_TRY(launch_spec4800(a, st));
+    CUDA_TRY(launch_get_end_scan(tab, (int)n_items, mm, L.chunk_stride, chunk_frames, d_out, st));
+    return CAC_OK;
+}

@@ -8,6 +8,8 @@
 // passes over the 75 rows, results written back in place) -> real-FFT untangle for the requested bins
 // only, read straight from the Z matrix in shared memory.  No staging buffer: samples come from
 // global memory (the overlap between neighbouring frames is served by L1/L2).
+#include <algorithm>
+
 #include "cac_common.cuh"
 #include "fft_regs.cuh"
 #include "spec.cuh"
@@ -146,8 +148,9 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
             if (a.frame_base[mid] <= g) lo = mid; else hi = mid - 1;
         }
     }
+    const long long n_total = a.n_frames_total >= 0 ? a.n_frames_total : a.frame_base[a.n_items];
 #pragma unroll 1
-    for (long long g = (long long)blockIdx.x * kWarps48 + warp; g < a.n_frames_total; g += stride) {
+    for (long long g = (long long)blockIdx.x * kWarps48 + warp; g < n_total; g += stride) {
         if (kWalk) {
             while (a.frame_base[lo + 1] <= g) ++lo;           // g < n_frames_total = frame_base[n_items]: stops in range
         } else {
@@ -234,6 +237,7 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
             for (int i = a.nbins + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;
             __syncwarp();
             float* oitem = a.out + (size_t)fbase * a.n_mels;
+            float fmn = INFINITY, fmx = 0.f;
 #pragma unroll 1
             for (int gidx = 0; gidx < a.n_groups; ++gidx) {
                 const int slot = mstart[gidx * 32 + lane];   // (band start) | row << 16, mel_bands.h
@@ -251,7 +255,17 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
                     acc = fmaf(w.z, q.z, acc);
                     acc = fmaf(w.w, q.w, acc);
                 }
-                if (live) oitem[(size_t)m * nfi + f] = acc;
+                if (a.chunk_mm) { if (live) { fmn = fminf(fmn, acc); fmx = fmaxf(fmx, acc); } }
+                else if (live) oitem[(size_t)m * nfi + f] = acc;
+            }
+            if (a.chunk_mm) {                                 // get_end: only the chunk's extrema are kept
+                fmn = warp_min(fmn);
+                fmx = warp_max(fmx);
+                if (lane == 0) {
+                    uint2* mm = a.chunk_mm + (size_t)lo * a.chunk_stride + f / a.chunk_frames;
+                    atomicMin(&mm->x, __float_as_uint(fmn));
+                    atomicMax(&mm->y, __float_as_uint(fmx));
+                }
             }
             __syncwarp();
         }
@@ -355,6 +369,40 @@ __global__ void __launch_bounds__(256) scale_by_max_kernel(float* __restrict__ d
         data[i] = __fdiv_rn(data[i], d);
 }
 
+// ---- get_end for a batch: device-built item tables and the first-silent-chunk scan ------------------------------
+__global__ void get_end_prep_kernel(const long long* __restrict__ off, const long long* __restrict__ len, int n, int n_fft,
+                                    int hop, long long max_len, long long* __restrict__ tab, uint2* __restrict__ mm,
+                                    int chunk_stride, int* __restrict__ out) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        long long total = 0;
+        for (int i = 0; i < n; ++i) {
+            const long long ns = max(0LL, min(len[i], max_len));
+            tab[i] = off[i];
+            tab[n + i] = ns;
+            tab[2 * n + i] = total;
+            const long long padded = ns + 2LL * (n_fft / 2);
+            total += padded >= n_fft ? 1 + (padded - n_fft) / hop : 0;
+        }
+        tab[3 * n] = total;
+    }
+    const long long cells = (long long)n * chunk_stride;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < cells; i += (long long)gridDim.x * blockDim.x)
+        mm[i] = make_uint2(0x7f800000u, 0u);                  // {+inf, 0}
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = -1;
+}
+
+// the reference's loop (src/identify_tracks.py:406-412): chunks [c L, (c + 1) L) while (c + 1) L < n_frames
+__global__ void get_end_scan_kernel(const long long* __restrict__ tab, int n, const uint2* __restrict__ mm, int chunk_stride,
+                                    int chunk_frames, int* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long nf = tab[2 * n + i + 1] - tab[2 * n + i];
+    for (int c = 0; (long long)(c + 1) * chunk_frames < nf; ++c) {
+        const uint2 v = mm[(size_t)i * chunk_stride + c];
+        if (v.x == v.y) { out[i] = c; return; }
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------
 void spec4800_host_tables(int n_fft, int kmin, float2* ltab, float2* rtab) {
     const long double tau = 6.283185307179586476925286766559005768L;
@@ -408,9 +456,25 @@ cudaError_t launch_spec4800(const SpecArgs& a, cudaStream_t st) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    long long grid = (a.n_frames_total + kWarps48 - 1) / kWarps48;
+    long long grid = a.n_frames_total >= 0 ? (a.n_frames_total + kWarps48 - 1) / kWarps48 : sms;
     if (grid > sms) grid = sms;
     kern<<<(unsigned)grid, kWarps48 * 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_get_end_prep(const long long* d_item_off, const long long* d_item_len, int n_items, int n_fft, int hop,
+                                long long max_item_samples, long long* tab, uint2* mm, int chunk_stride, int* out,
+                                cudaStream_t st) {
+    const long long cells = (long long)n_items * chunk_stride;
+    const unsigned blocks = (unsigned)std::min<long long>(std::max<long long>((cells + 255) / 256, 1), 1024);
+    get_end_prep_kernel<<<blocks, 256, 0, st>>>(d_item_off, d_item_len, n_items, n_fft, hop, max_item_samples, tab, mm,
+                                                chunk_stride, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_get_end_scan(const long long* tab, int n_items, const uint2* mm, int chunk_stride, int chunk_frames,
+                                int* out, cudaStream_t st) {
+    get_end_scan_kernel<<<(unsigned)((n_items + 127) / 128), 128, 0, st>>>(tab, n_items, mm, chunk_stride, chunk_frames, out);
     return cudaGetLastError();
 }
 

@@ -3,188 +3,19 @@
 // Replaces, for every segment of load_samples' loop (src/identify_tracks.py:163-190):
 //   normalize_data (:202-209) -> librosa.stft(n_fft=4096, hop) (:243) -> |.|**power
 //   (src/custommel.py:61) -> mel_f(...).dot(magnitude) (src/custommel.py:62-63)
-// The [2049 x frames] spectrum never leaves the SM: one warp transforms one frame
-// (4096 real points = 2048-point complex FFT as radix-64 x radix-32 in registers with a
-// single shared-memory transpose), the power spectrum of a 32-frame tile is parked in
-// shared memory and the sparse triangular filterbank is applied as banded dot products
-// with lanes = frames (conflict-free, weights broadcast from constant memory).
+// The [2049 x frames] spectrum never leaves the SM: one warp transforms one frame (fft4096.cuh:
+// 4096 real points = 2048-point complex FFT as radix-64 x radix-32 in registers with a single
+// shared-memory transpose) and parks the frame's power spectrum in its own shared-memory buffer;
+// the sparse triangular filterbank is applied by the same warp as banded dot products with
+// lanes = mel rows (128-bit loads of zero-padded tap-major weights kept in shared memory), and the
+// CTA writes each stage's mel values as contiguous row segments.
 #include "cac_common.cuh"
-#include "fft_regs.cuh"
+#include "fft4096.cuh"
 
 namespace cac {
 
 __constant__ BandTable c_bands;
 __constant__ float c_weights[kMaxTaps];
-
-constexpr int kNfft = 4096;
-constexpr int kExStride = 33;                 // floats per exchange row (odd -> conflict-free transpose)
-constexpr int kExFloats = 2 * 32 * kExStride; // one warp's exchange buffer: 32 rows x 33 float2
-constexpr int kWarpsPerCta = 12;               // 12 warps x 168 registers fill the register file
-
-// ---- pass 1 input: 64 complex points z[32*i + lane] = (x[2n], x[2n+1]) * Hann ------------
-// Hann(s) = 0.5 - 0.5 cos(2 pi s / 4096) with s = 64*i + (2*lane + e): the cosine of the sum is
-// expanded so that the i-part is a compile-time constant and the lane part sits in 4 registers.
-template <int I>
-struct WinLoad {
-    static __device__ __forceinline__ void run(float (&re)[64], float (&im)[64], const float* pe,
-                                               const float* po, float hcb0, float hsb0, float hcb1,
-                                               float hsb1) {
-        constexpr float ca = (float)cx_cos2pi(I, 64);
-        constexpr float sa = (float)cx_sin2pi(I, 64);
-        float w0 = fmaf(-ca, hcb0, fmaf(sa, hsb0, 0.5f));
-        float w1 = fmaf(-ca, hcb1, fmaf(sa, hsb1, 0.5f));
-        re[I] = pe[32 * I] * w0;
-        im[I] = po[32 * I] * w1;
-        if constexpr (I + 1 < 64) WinLoad<I + 1>::run(re, im, pe, po, hcb0, hsb0, hcb1, hsb1);
-    }
-};
-
-// ---- transpose through shared memory: row k1 (pass-1 output index), column n2 (= lane) -----
-// The buffer holds 32 rows of 33 float2 (re, im); rows k1 = 0..31 go through first, then rows 32..63,
-// so each transfer is a 64-bit shared-memory access (half the instructions of separate re/im planes).
-template <int K1, int BASE>
-struct ExWrite {
-    static __device__ __forceinline__ void run(const float (&vr)[64], const float (&vi)[64], float2* ex_lane) {
-        ex_lane[K1 * kExStride] = make_float2(vr[out_pos(64, BASE + K1)], vi[out_pos(64, BASE + K1)]);
-        if constexpr (K1 + 1 < 32) ExWrite<K1 + 1, BASE>::run(vr, vi, ex_lane);
-    }
-};
-template <int N2>
-struct ExRead {
-    static __device__ __forceinline__ void run(float (&vr)[32], float (&vi)[32], const float2* ex_row) {
-        const float2 t = ex_row[N2];
-        vr[N2] = t.x;
-        vi[N2] = t.y;
-        if constexpr (N2 + 1 < 32) ExRead<N2 + 1>::run(vr, vi, ex_row);
-    }
-};
-
-// ---- pass 2 twiddles: W2048^(k1*n2), k1 = lane + 32*H  ==  Tw_lane[n2] * W64^(H*n2) ----------
-// Tw_lane[n2] = exp(-2 pi i lane n2 / 2048) is kept as a two-level product A[n2>>3] * B[n2&7]
-// (3 + 7 complex registers instead of 31: keeps the kernel free of register spills).
-struct Twid {
-    float ar[4], ai[4];   // n2 = 0, 8, 16, 24
-    float br[8], bi[8];   // n2 = 0..7
-};
-// one half at a time (H = 0: z0, H = 1: z1 with the extra W64^(N2)): lets the first half's multiplies run
-// while the second half is still moving through shared memory, at the price of forming A*B twice
-template <int N2, int H>
-struct Pass2TwHalf {
-    static __device__ __forceinline__ void run(float (&zr)[32], float (&zi)[32], const Twid& tw) {
-        if constexpr (N2 > 0) {
-            constexpr int A = N2 >> 3, B = N2 & 7;
-            float tr, ti;
-            if constexpr (A == 0) { tr = tw.br[B]; ti = tw.bi[B]; }
-            else if constexpr (B == 0) { tr = tw.ar[A]; ti = tw.ai[A]; }
-            else {
-                tr = fmaf(-tw.ai[A], tw.bi[B], tw.ar[A] * tw.br[B]);
-                ti = fmaf(tw.ar[A], tw.bi[B], tw.ai[A] * tw.br[B]);
-            }
-            float xr = zr[N2], xi = zi[N2];
-            if constexpr (H == 1) mul_twiddle<N2, 64>(xr, xi);
-            zr[N2] = fmaf(-xi, ti, xr * tr);
-            zi[N2] = fmaf(xr, ti, xi * tr);
-        }
-        if constexpr (N2 + 1 < 32) Pass2TwHalf<N2 + 1, H>::run(zr, zi, tw);
-    }
-};
-
-// ---- real-FFT untangle + power, bins k = lane + 32*H + 64*K2 ---------------------------------
-// X[k] = (Z[k] + conj Z[2048-k])/2 - (i/2) W4096^k (Z[k] - conj Z[2048-k]); Z[2048-k] lives in
-// lane (32-lane)&31 (other half, index 31-K2), fetched with one shuffle per component.
-template <int K2, int H, int K2N, int POWER>
-struct Untangle {
-    static __device__ __forceinline__ void run(const float (&z0r)[32], const float (&z0i)[32],
-                                               const float (&z1r)[32], const float (&z1i)[32], int lane,
-                                               int partner, float bc, float bs, float* pbuf_lane) {
-        constexpr int pown = out_pos(32, K2);
-        constexpr int psend = out_pos(32, 31 - K2);
-        constexpr int psend0 = out_pos(32, (32 - K2) & 31);
-        float ar = H ? z1r[pown] : z0r[pown];
-        float ai = H ? z1i[pown] : z0i[pown];
-        // value this lane sends: the opposite half (lane 0 is its own partner and stays in its half)
-        float sr, si;
-        if constexpr (H == 0) {
-            sr = (lane == 0) ? z0r[psend0] : z1r[psend];
-            si = (lane == 0) ? z0i[psend0] : z1i[psend];
-        } else {
-            sr = (lane == 0) ? z1r[psend] : z0r[psend];
-            si = (lane == 0) ? z1i[psend] : z0i[psend];
-        }
-        float br = __shfl_sync(0xffffffffu, sr, partner);
-        float bi = -__shfl_sync(0xffffffffu, si, partner);   // conj
-        float sumr = ar + br, sumi = ai + bi;
-        float dr = ar - br, di = ai - bi;
-        mul_twiddle<K2, 64>(dr, di);                         // W4096^(64*K2)
-        float tr = fmaf(di, bs, dr * bc);                    // * W4096^(lane + 32H) = (bc, -bs)
-        float ti = fmaf(-dr, bs, di * bc);
-        // 2 X[k]: the factor 1/2 of the untangle (1/4 of the power) is folded into the mel weights on the host
-        float xr = sumr + ti;
-        float xi = sumi - tr;
-        float p = fmaf(xr, xr, xi * xi);
-        if constexpr (POWER == 1) p = sqrtf(p);
-        pbuf_lane[32 * H + 64 * K2] = p;                   // pbuf is indexed by the absolute bin: no range checks
-        if constexpr (K2 + 1 < K2N)
-            Untangle<K2 + 1, H, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, bc, bs, pbuf_lane);
-    }
-};
-
-struct LaneConsts {
-    float hcb0, hsb0, hcb1, hsb1;   // 0.5*cos / 0.5*sin of 2 pi (2 lane + e)/4096
-    float bc0, bs0, bc1, bs1;       // cos / sin of 2 pi (lane + 32 h)/4096
-};
-
-// One warp: Hann-windowed 4096-point real FFT of the frame starting at staged sample u0,
-// power spectrum of bins [0, 64 K2N) written to the warp's own buffer pbuf[bin].
-template <int POWER, int K2N>
-__device__ __forceinline__ void fft_frame(const float* __restrict__ se, const float* __restrict__ so, int u0,
-                                          float* __restrict__ ex, float* __restrict__ pbuf, int lane,
-                                          const float* __restrict__ lt) {
-    // lt: per-lane constants parked in shared memory ([28][32], see stft_mel_kernel) and re-read per
-    // frame so they do not occupy registers next to the 128 data registers of the FFT
-    float ar[64], ai[64];
-    {
-        const float* pe;
-        const float* po;
-        if (u0 & 1) { pe = so + (u0 >> 1) + lane; po = se + ((u0 + 1) >> 1) + lane; }
-        else        { pe = se + (u0 >> 1) + lane; po = so + (u0 >> 1) + lane; }
-        WinLoad<0>::run(ar, ai, pe, po, lt[0 * 32], lt[1 * 32], lt[2 * 32], lt[3 * 32]);
-    }
-    fft_dif<64>(ar, ai);
-
-    float z0r[32], z0i[32], z1r[32], z1i[32];
-    float2* ex2 = reinterpret_cast<float2*>(ex);
-    __syncwarp();
-    ExWrite<0, 0>::run(ar, ai, ex2 + lane);
-    __syncwarp();
-    ExRead<0>::run(z0r, z0i, ex2 + lane * kExStride);
-    __syncwarp();
-    ExWrite<0, 32>::run(ar, ai, ex2 + lane);
-    __syncwarp();
-    ExRead<0>::run(z1r, z1i, ex2 + lane * kExStride);
-    Twid tw;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { tw.ar[j] = lt[(8 + j) * 32]; tw.ai[j] = lt[(12 + j) * 32]; }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { tw.br[j] = lt[(16 + j) * 32]; tw.bi[j] = lt[(24 + j) * 32]; }
-    Pass2TwHalf<0, 0>::run(z0r, z0i, tw);      // independent of the loads above: runs while they are in flight
-    __syncwarp();   // pbuf aliases ex: nobody may still be reading the exchange rows when the power values land
-    Pass2TwHalf<0, 1>::run(z1r, z1i, tw);
-    fft_dif<32>(z0r, z0i);
-    fft_dif<32>(z1r, z1i);
-
-    const int partner = (32 - lane) & 31;
-    Untangle<0, 0, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[4 * 32], lt[5 * 32], pbuf + lane);
-    Untangle<0, 1, K2N, POWER>::run(z0r, z0i, z1r, z1i, lane, partner, lt[6 * 32], lt[7 * 32], pbuf + lane);
-}
-
-__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
-    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-    int nbytes = valid ? 4 : 0;                    // 0 source bytes -> the 4 destination bytes are zero-filled
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(nbytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Shared-memory carve-up of stft_mel_kernel (floats unless noted); the launcher uses the same function.
 struct FeatSmem {
@@ -212,7 +43,7 @@ __host__ __device__ inline FeatSmem feat_smem_layout(int stage_half, int n_taps,
     return L;
 }
 
-// Persistent kernel, one CTA (8 warps) per SM.  Work unit = a "stage": frames_per_stage consecutive
+// Persistent kernel, one CTA (12 warps) per SM.  Work unit = a "stage": frames_per_stage consecutive
 // frames of one segment.  The samples of stage q+1 are fetched with cp.async (zero-filled outside the
 // real samples) straight into the other pair of even / odd sample planes while the warps transform
 // stage q; each warp owns whole frames: FFT -> power spectrum (own buffer) -> banded mel gather -> tile.
@@ -232,21 +63,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
     // ---- one-time tables ------------------------------------------------------------------------
     for (int i = tid; i < a.n_taps; i += kWarpsPerCta * 32) wts[i] = a.wpad[i];
     for (int m = tid; m < a.n_groups * 32; m += kWarpsPerCta * 32) slots[m] = reinterpret_cast<const int4*>(a.mstart)[m];
-    if (warp == 0) {   // per-lane constants: rows 0-3 window, 4-7 untangle, 8-31 two-level twiddles
-        float s, c;
-        sincospif((float)(2 * lane) / 2048.0f, &s, &c);      ltab[0 * 32 + lane] = 0.5f * c; ltab[1 * 32 + lane] = 0.5f * s;
-        sincospif((float)(2 * lane + 1) / 2048.0f, &s, &c);  ltab[2 * 32 + lane] = 0.5f * c; ltab[3 * 32 + lane] = 0.5f * s;
-        sincospif((float)lane / 2048.0f, &s, &c);            ltab[4 * 32 + lane] = c; ltab[5 * 32 + lane] = s;
-        sincospif((float)(lane + 32) / 2048.0f, &s, &c);     ltab[6 * 32 + lane] = c; ltab[7 * 32 + lane] = s;
-        for (int j = 0; j < 4; ++j) {                         // exp(-2 pi i lane (8j) / 2048)
-            sincospif((float)(lane * 8 * j) / 1024.0f, &s, &c);
-            ltab[(8 + j) * 32 + lane] = c; ltab[(12 + j) * 32 + lane] = -s;
-        }
-        for (int j = 0; j < 8; ++j) {                         // exp(-2 pi i lane j / 2048)
-            sincospif((float)(lane * j) / 1024.0f, &s, &c);
-            ltab[(16 + j) * 32 + lane] = c; ltab[(24 + j) * 32 + lane] = -s;
-        }
-    }
+    if (warp == 0) init_lane_table(ltab, lane);
     const float* lt = ltab + lane;
 
     const long long n_stages = a.n_segs * a.stages_per_seg;
@@ -299,11 +116,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
             const float* sp = otile + m * tstride + f;
             const size_t gstep = (size_t)rows_per_iter * a.n_frames;
             const int sstep = rows_per_iter * tstride;
-            for (; m < a.n_mels; m += rows_per_iter, gp += gstep, sp += sstep) *gp = *sp;
+            if (a.mag_on) { for (; m < a.n_mels; m += rows_per_iter, gp += gstep, sp += sstep) *gp = powf(*sp, a.mag_p); }
+            else { for (; m < a.n_mels; m += rows_per_iter, gp += gstep, sp += sstep) *gp = *sp; }
         } else {
             for (int t = tid; t < a.n_mels * nfs; t += kThreads) {
                 const int m = t / nfs, f = t - m * nfs;
-                outseg[(size_t)m * a.n_frames + f] = otile[m * tstride + f];
+                const float v = otile[m * tstride + f];
+                outseg[(size_t)m * a.n_frames + f] = a.mag_on ? powf(v, a.mag_p) : v;
             }
         }
     };

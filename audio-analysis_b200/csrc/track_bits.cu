@@ -5,8 +5,10 @@
 // shifts, the vertical passes word-wise OR / AND, and the components are built from horizontal RUNS (a label
 // per run start, unions only between runs of adjacent rows), a few thousand objects instead of millions.
 // Bit i of word w of a row = pixel 32 w + i; the padding bits of the last word of a row are always 0.
+// Every kernel works on a WAVE of recordings (sn.cuh): recording = blockIdx.z, its geometry comes from the item table,
+// its masks / labels / result block from slot blockIdx.z of the wave's scratch arrays.
 #include "cac_common.cuh"
-#include "track_signals.cuh"
+#include "sn.cuh"
 
 namespace cac {
 
@@ -15,35 +17,21 @@ __device__ __forceinline__ unsigned valid_bits(int w, long long cols) {   // pix
     return left >= 32 ? 0xffffffffu : (left <= 0 ? 0u : ((1u << (int)left) - 1u));
 }
 
-// ---- signal = (spec > 3 * column_medians) & (spec > 3 * row_medians)  (:667), 32 pixels per ballot ----
-__global__ void __launch_bounds__(256) signal_mask_bits_kernel(const float* __restrict__ spec,
-                                                               const float* __restrict__ rowmed,
-                                                               const float* __restrict__ colmed,
-                                                               unsigned* __restrict__ bits, int rows, long long cols,
-                                                               int wpr) {
-    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
-    const int r = blockIdx.y;
-    bool on = false;
-    if (c < cols) {
-        const float v = spec[(size_t)r * cols + c];
-        const float tc = __fmul_rn(3.0f, colmed[c]), tr = __fmul_rn(3.0f, rowmed[r]);
-        on = v > tc && v > tr;
-    }
-    const unsigned word = __ballot_sync(0xffffffffu, on);
-    const long long w = c >> 5;
-    if ((threadIdx.x & 31) == 0 && w < wpr) bits[(size_t)r * wpr + w] = word;
-}
-
 // ---- cv2.erode / cv2.dilate with a 1 x k rectangle: out(x) = OR | AND over d in [0, k) of in(x - k/2 + d) ----
 // pixels outside the image are ignored (cv2's morphology border).  Erosion runs as the complement of the
 // dilation of the complement (outside = 0 in the complemented domain is exactly "ignored").
 template <bool IS_MAX>
-__global__ void __launch_bounds__(128) morph_h_bits_kernel(const unsigned* __restrict__ in, unsigned* __restrict__ out,
-                                                           long long cols, int wpr, int k) {
+__global__ void __launch_bounds__(128) morph_h_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     extern __shared__ unsigned seg[];                 // words w0 - halo .. w0 + 127 + halo of this row
+    const SnItem im = wv.items[blockIdx.z];
+    const int wpr = im.wpr;
+    const long long cols = im.cols;
     const int halo = (k + 31) / 32 + 1;
     const int w0 = blockIdx.x * 128;
+    if (w0 >= wpr) return;                            // shorter recording of the wave (uniform for the CTA)
     const int r = blockIdx.y;
+    const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
+    unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
     const unsigned* row = in + (size_t)r * wpr;
     for (int i = threadIdx.x; i < 128 + 2 * halo; i += 128) {
         const int w = w0 - halo + i;
@@ -71,8 +59,11 @@ __global__ void __launch_bounds__(128) morph_h_bits_kernel(const unsigned* __res
 
 // ---- k x 1 rectangle: OR | AND over the rows r - k/2 .. r - k/2 + k - 1 that exist --------------------
 template <bool IS_MAX>
-__global__ void __launch_bounds__(128) morph_v_bits_kernel(const unsigned* __restrict__ in, unsigned* __restrict__ out,
-                                                           int rows, int wpr, int k) {
+__global__ void __launch_bounds__(128) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
+    const int wpr = wv.items[blockIdx.z].wpr;
+    const int rows = wv.rows;
+    const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
+    unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
     const int w = blockIdx.x * 128 + threadIdx.x;
     const int r = blockIdx.y;
     if (w >= wpr) return;
@@ -85,8 +76,13 @@ __global__ void __launch_bounds__(128) morph_v_bits_kernel(const unsigned* __res
     out[(size_t)r * wpr + w] = acc;
 }
 
-__global__ void __launch_bounds__(256) unpack_bits_kernel(const unsigned* __restrict__ bits, unsigned char* __restrict__ out,
-                                                          long long cols, int wpr) {
+__global__ void __launch_bounds__(256) unpack_bits_kernel(const SnWave wv, int plane, unsigned char* __restrict__ out_all,
+                                                          long long out_stride) {
+    const SnItem im = wv.items[blockIdx.z];
+    const long long cols = im.cols;
+    const int wpr = im.wpr;
+    const unsigned* bits = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)plane * wv.plane_stride;
+    unsigned char* out = out_all + (size_t)blockIdx.z * out_stride;
     const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
     const int r = blockIdx.y;
     if (c >= cols) return;
@@ -115,10 +111,16 @@ __device__ __forceinline__ int run_start(const unsigned* row, int x) {          
     }
     return 32 * w + (32 - __clz(z));
 }
+// label[p] >= 0: parent of run start p (p itself for a root); label[p] < 0: p is a numbered root, id = -1 - label[p]
 __device__ __forceinline__ int uf_find(const int* label, int a) {
     int p = label[a];
     while (p != a) { a = p; p = label[a]; }
     return a;
+}
+__device__ __forceinline__ int uf_find_id(const int* label, int a) {     // after runs_roots_kernel
+    int p = label[a];
+    while (p >= 0) { a = p; p = label[a]; }
+    return -1 - p;
 }
 __device__ __forceinline__ void uf_union(int* label, int a, int b) {
     while (true) {
@@ -138,26 +140,45 @@ __device__ __forceinline__ unsigned start_bits(const unsigned* row, int w) {
     return v & ~((v << 1) | prev);
 }
 
-__global__ void __launch_bounds__(128) runs_init_kernel(const unsigned* __restrict__ bits, int* __restrict__ label, int rows,
-                                                        int cols, int wpr) {
+struct CclView {                                  // recording blockIdx.z of the wave
+    const unsigned* bits;
+    int* label;
+    int* result;
+    int cols, wpr;
+};
+__device__ __forceinline__ CclView ccl_view(const SnWave& wv, int plane) {
+    const SnItem im = wv.items[blockIdx.z];
+    CclView v;
+    v.bits = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)plane * wv.plane_stride;
+    v.label = wv.label + (size_t)blockIdx.z * wv.label_stride;
+    v.result = wv.result + (size_t)blockIdx.z * wv.result_stride;
+    v.cols = im.cols;
+    v.wpr = im.wpr;
+    return v;
+}
+
+__global__ void __launch_bounds__(128) runs_init_kernel(const SnWave wv, int plane) {
+    const CclView v = ccl_view(wv, plane);
     const int w = blockIdx.x * 128 + threadIdx.x;
     const int y = blockIdx.y;
-    if (w >= wpr) return;
-    unsigned s = start_bits(bits + (size_t)y * wpr, w);
+    if (w >= v.wpr) return;
+    unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
     while (s) {
         const int x = 32 * w + __ffs(s) - 1;
         s &= s - 1;
-        label[y * cols + x] = y * cols + x;
+        v.label[y * v.cols + x] = y * v.cols + x;
     }
 }
 
 // every run is joined with the runs of the row above that touch [xs - 1, xe + 1] (8-connectivity)
-__global__ void __launch_bounds__(128) runs_merge_kernel(const unsigned* __restrict__ bits, int* __restrict__ label, int rows,
-                                                         int cols, int wpr) {
+__global__ void __launch_bounds__(128) runs_merge_kernel(const SnWave wv, int plane) {
+    const CclView v = ccl_view(wv, plane);
+    const int wpr = v.wpr, cols = v.cols;
+    int* label = v.label;
     const int w = blockIdx.x * 128 + threadIdx.x;
     const int y = blockIdx.y + 1;
-    if (w >= wpr || y >= rows) return;
-    const unsigned* row = bits + (size_t)y * wpr;
+    if (w >= wpr || y >= wv.rows) return;
+    const unsigned* row = v.bits + (size_t)y * wpr;
     const unsigned* up = row - wpr;
     unsigned s = start_bits(row, w);
     while (s) {
@@ -181,40 +202,37 @@ __global__ void __launch_bounds__(128) runs_merge_kernel(const unsigned* __restr
     }
 }
 
-// roots get consecutive ids (arbitrary order); rootid[] is valid at root positions only
-__global__ void __launch_bounds__(128) runs_roots_kernel(const unsigned* __restrict__ bits, const int* __restrict__ label,
-                                                         int* __restrict__ rootid, int rows, int cols, int wpr,
-                                                         int* __restrict__ counter, int max_components) {
+// roots get consecutive ids (arbitrary order), written in place as -1 - id; result[0] counts them (a count above
+// max_components marks the recording's table as overflowed - its stats rows beyond the limit are never written)
+__global__ void __launch_bounds__(128) runs_roots_kernel(const SnWave wv, int plane) {
+    const CclView v = ccl_view(wv, plane);
     const int w = blockIdx.x * 128 + threadIdx.x;
     const int y = blockIdx.y;
-    if (w >= wpr) return;
-    unsigned s = start_bits(bits + (size_t)y * wpr, w);
+    if (w >= v.wpr) return;
+    unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
     while (s) {
-        const int p = y * cols + 32 * w + __ffs(s) - 1;
+        const int p = y * v.cols + 32 * w + __ffs(s) - 1;
         s &= s - 1;
-        if (label[p] == p) {
-            const int id = atomicAdd(counter, 1);
-            rootid[p] = id < max_components ? id : -1;
-        }
+        if (v.label[p] == p) v.label[p] = -1 - atomicAdd(v.result, 1);
     }
 }
 
 // stats[id] = {min x, min y, max x, max y, area, first 2x2 block in raster order}, one update per run
-__global__ void __launch_bounds__(128) runs_stats_kernel(const unsigned* __restrict__ bits, const int* __restrict__ label,
-                                                         const int* __restrict__ rootid, int rows, int cols, int wpr,
-                                                         int* __restrict__ stats) {
+__global__ void __launch_bounds__(128) runs_stats_kernel(const SnWave wv, int plane) {
+    const CclView v = ccl_view(wv, plane);
+    const int wpr = v.wpr, cols = v.cols;
     const int w = blockIdx.x * 128 + threadIdx.x;
     const int y = blockIdx.y;
     if (w >= wpr) return;
-    const unsigned* row = bits + (size_t)y * wpr;
+    const unsigned* row = v.bits + (size_t)y * wpr;
     unsigned s = start_bits(row, w);
     while (s) {
         const int xs = 32 * w + __ffs(s) - 1;
         s &= s - 1;
         const int xe = run_end(row, wpr, xs);
-        const int id = rootid[uf_find(label, y * cols + xs)];
-        if (id < 0) continue;
-        int* st = stats + 6 * id;
+        const int id = uf_find_id(v.label, y * cols + xs);
+        if (id >= wv.max_components) continue;
+        int* st = v.result + 4 + 6 * id;
         atomicMin(st + 0, xs);
         atomicMin(st + 1, y);
         atomicMax(st + 2, xe);
@@ -224,58 +242,49 @@ __global__ void __launch_bounds__(128) runs_stats_kernel(const unsigned* __restr
     }
 }
 
-__global__ void __launch_bounds__(256) stats_init_kernel(int* stats, int max_components) {
+__global__ void __launch_bounds__(256) stats_init_kernel(const SnWave wv) {
+    int* result = wv.result + (size_t)blockIdx.y * wv.result_stride;
     const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i >= max_components) return;
-    int* s = stats + 6 * i;
+    if (i < 4) result[i] = 0;                         // [0] = component counter
+    if (i >= wv.max_components) return;
+    int* s = result + 4 + 6 * i;
     s[0] = 0x7fffffff; s[1] = 0x7fffffff; s[2] = -1; s[3] = -1; s[4] = 0; s[5] = 0x7fffffff;
 }
 
-// ---- launchers --------------------------------------------------------------------------------------
-cudaError_t launch_signal_mask_bits(const float* spec, const float* rowmed, const float* colmed, unsigned* bits, int rows,
-                                    long long cols, cudaStream_t st) {
-    const int wpr = (int)((cols + 31) / 32);
-    dim3 grid((unsigned)((cols + 255) / 256), (unsigned)rows);
-    signal_mask_bits_kernel<<<grid, 256, 0, st>>>(spec, rowmed, colmed, bits, rows, cols, wpr);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_morph_rect_bits(const unsigned* in, unsigned* tmp, unsigned* out, int rows, long long cols, int kh,
-                                   int kw, bool is_max, cudaStream_t st) {
-    const int wpr = (int)((cols + 31) / 32);
-    dim3 grid((unsigned)((wpr + 127) / 128), (unsigned)rows);
+// ---- launchers (whole wave per launch) ---------------------------------------------------------------------
+// out = erode (is_max = false) / dilate (true) of plane `src` with a kh x kw rectangle; `tmp` is scratch
+cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp_plane, int dst_plane, int max_wpr, int kh,
+                                         int kw, bool is_max, cudaStream_t st) {
+    dim3 grid((unsigned)((max_wpr + 127) / 128), (unsigned)w.rows, (unsigned)w.n_items);
     const size_t smem = (128 + 2 * ((kw + 31) / 32 + 1)) * sizeof(unsigned);
     if (is_max) {
-        morph_h_bits_kernel<true><<<grid, 128, smem, st>>>(in, tmp, cols, wpr, kw);
-        morph_v_bits_kernel<true><<<grid, 128, 0, st>>>(tmp, out, rows, wpr, kh);
+        morph_h_bits_kernel<true><<<grid, 128, smem, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<true><<<grid, 128, 0, st>>>(w, tmp_plane, dst_plane, kh);
     } else {
-        morph_h_bits_kernel<false><<<grid, 128, smem, st>>>(in, tmp, cols, wpr, kw);
-        morph_v_bits_kernel<false><<<grid, 128, 0, st>>>(tmp, out, rows, wpr, kh);
+        morph_h_bits_kernel<false><<<grid, 128, smem, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<false><<<grid, 128, 0, st>>>(w, tmp_plane, dst_plane, kh);
     }
     return cudaGetLastError();
 }
 
-cudaError_t launch_unpack_bits(const unsigned* bits, unsigned char* out, int rows, long long cols, cudaStream_t st) {
-    const int wpr = (int)((cols + 31) / 32);
-    dim3 grid((unsigned)((cols + 255) / 256), (unsigned)rows);
-    unpack_bits_kernel<<<grid, 256, 0, st>>>(bits, out, cols, wpr);
+cudaError_t launch_unpack_bits_batch(const SnWave& w, int plane, unsigned char* out, long long out_stride, int max_cols,
+                                     cudaStream_t st) {
+    dim3 grid((unsigned)((max_cols + 255) / 256), (unsigned)w.rows, (unsigned)w.n_items);
+    unpack_bits_kernel<<<grid, 256, 0, st>>>(w, plane, out, out_stride);
     return cudaGetLastError();
 }
 
-cudaError_t launch_ccl_runs(const unsigned* bits, int* label, int* rootid, int rows, int cols, int* counter, int* stats,
-                            int max_components, cudaStream_t st) {
-    const int wpr = (cols + 31) / 32;
-    dim3 grid((unsigned)((wpr + 127) / 128), (unsigned)rows);
-    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), st);
-    if (e != cudaSuccess) return e;
-    stats_init_kernel<<<(max_components + 255) / 256, 256, 0, st>>>(stats, max_components);
-    runs_init_kernel<<<grid, 128, 0, st>>>(bits, label, rows, cols, wpr);
-    if (rows > 1) {
-        dim3 gridm((unsigned)((wpr + 127) / 128), (unsigned)(rows - 1));
-        runs_merge_kernel<<<gridm, 128, 0, st>>>(bits, label, rows, cols, wpr);
+cudaError_t launch_ccl_runs_batch(const SnWave& w, int plane, int max_wpr, cudaStream_t st) {
+    dim3 grid((unsigned)((max_wpr + 127) / 128), (unsigned)w.rows, (unsigned)w.n_items);
+    const int init_n = w.max_components > 4 ? w.max_components : 4;
+    stats_init_kernel<<<dim3((unsigned)((init_n + 255) / 256), (unsigned)w.n_items), 256, 0, st>>>(w);
+    runs_init_kernel<<<grid, 128, 0, st>>>(w, plane);
+    if (w.rows > 1) {
+        dim3 gridm(grid.x, (unsigned)(w.rows - 1), grid.z);
+        runs_merge_kernel<<<gridm, 128, 0, st>>>(w, plane);
     }
-    runs_roots_kernel<<<grid, 128, 0, st>>>(bits, label, rootid, rows, cols, wpr, counter, max_components);
-    runs_stats_kernel<<<grid, 128, 0, st>>>(bits, label, rootid, rows, cols, wpr, stats);
+    runs_roots_kernel<<<grid, 128, 0, st>>>(w, plane);
+    runs_stats_kernel<<<grid, 128, 0, st>>>(w, plane);
     return cudaGetLastError();
 }
 

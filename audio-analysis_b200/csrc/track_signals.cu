@@ -1,6 +1,7 @@
-// signal_noise after its STFT (src/identify_tracks.py:658-666): exact row / column medians of the
-// normalised magnitude spectrogram ([2049 x frames], 84 MB per minute, mostly L2-resident).  The mask,
-// morphology and connected-component stages that follow (:667-686) work on a bit-packed mask: track_bits.cu.
+// Generic pieces of signal_noise's median stage (src/identify_tracks.py:658-659) for a spectrogram the CALLER
+// supplies (cac_signal_components_run): a tiled transpose and an exact row median, i.e. column medians as row
+// medians of the transposed matrix.  The batched chain does not use them: its column medians come out of the
+// spectrum kernel (sn_stft.cu) and its row medians are fused with the mask (sn_rows.cu).
 #include "cac_common.cuh"
 #include "track_signals.cuh"
 

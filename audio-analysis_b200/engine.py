@@ -42,6 +42,7 @@ lib.cac_plan_destroy.argtypes = [_vp]
 lib.cac_plan_frames.argtypes = [_vp]
 lib.cac_plan_set_profiling.argtypes = [_vp, ctypes.c_int]
 lib.cac_plan_last_kernel_ms.argtypes = [_vp, ctypes.POINTER(ctypes.c_float)]
+lib.cac_plan_set_magtransform.argtypes = [_vp, ctypes.c_int, ctypes.c_float]
 lib.cac_features_work_bytes.argtypes = [_vp, _i64]
 lib.cac_features_work_bytes.restype = ctypes.c_size_t
 lib.cac_features_run.argtypes = [_vp, _vp, _vp, _i64, _vp, _vp, _vp]
@@ -77,8 +78,20 @@ lib.cac_scale_by_max_run.argtypes = [_vp, _i64, _vp, _vp]
 lib.cac_chunk_minmax_run.argtypes = [_vp, _i32, _i64, _i32, _vp, _vp]
 lib.cac_morepork_windows_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp]
 
-lib.cac_signal_components.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]
-lib.cac_signal_components_async.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp]
+lib.cac_sn_plan_create.argtypes = [_i32, _i32, _i32, _i32, ctypes.c_int, ctypes.POINTER(_vp)]
+lib.cac_sn_plan_destroy.argtypes = [_vp]
+lib.cac_sn_frame_count.argtypes = [_vp, _i64]
+lib.cac_sn_frame_count.restype = _i64
+lib.cac_sn_work_bytes.argtypes = [_vp, _i64, _i64]
+lib.cac_sn_work_bytes.restype = ctypes.c_size_t
+lib.cac_sn_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _vp, _vp, ctypes.c_size_t, _vp]
+lib.cac_sn_spectrum_run.argtypes = [_vp, _vp, _i64, _vp, _vp, _vp, _vp, ctypes.c_size_t, _vp]
+lib.cac_signal_components_work_bytes.argtypes = [_i32, _i64]
+lib.cac_signal_components_work_bytes.restype = ctypes.c_size_t
+lib.cac_signal_components_run.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, ctypes.c_size_t, _vp]
+lib.cac_get_end_work_bytes.argtypes = [_vp, _i64, _i64, _i32]
+lib.cac_get_end_work_bytes.restype = ctypes.c_size_t
+lib.cac_get_end_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _vp, _vp, ctypes.c_size_t, _vp]
 lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
@@ -89,10 +102,10 @@ lib.cac_resample_out_len.argtypes = [_vp, _i64]
 lib.cac_resample_out_len.restype = _i64
 lib.cac_resample_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 
-EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_signal_components", "cac_signal_components_async", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
+EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_sn_plan_create", "cac_sn_plan_destroy", "cac_sn_frame_count", "cac_sn_work_bytes", "cac_sn_run", "cac_sn_spectrum_run", "cac_signal_components_work_bytes", "cac_signal_components_run", "cac_get_end_work_bytes", "cac_get_end_run", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
-           "cac_plan_frames", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
+           "cac_plan_frames", "cac_plan_set_magtransform", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
 
 
@@ -149,6 +162,10 @@ class FeaturePlan:
 
     def set_profiling(self, enable=True):
         check(lib.cac_plan_set_profiling(self._h, int(enable)))
+
+    def set_magtransform(self, a=None):
+        """Fuse MagTransform (y = x ** sigmoid(a)) into the kernel's output stage; a=None switches it off."""
+        check(lib.cac_plan_set_magtransform(self._h, int(a is not None), float(a or 0.0)))
 
     def last_kernel_ms(self):
         ms = ctypes.c_float()
@@ -350,6 +367,7 @@ class SpecPlan:
         check(lib.cac_spec_plan_create(ctypes.byref(self.params), w.ctypes.data_as(_vp) if w is not None else None,
                                        device, ctypes.byref(self._h)))
         self.rows = int(lib.cac_spec_rows(self._h))
+        self._work = None
 
     def close(self):
         if self._h:
@@ -384,6 +402,28 @@ class SpecPlan:
             check(lib.cac_spec_run(self._h, pcm.data_ptr(), off.ctypes.data_as(_vp), ns.ctypes.data_as(_vp), len(off),
                                    out.data_ptr(), mx.data_ptr() if want_max else None, _stream_ptr(torch)))
         return (out, base, mx) if want_max else (out, base)
+
+    def get_end_chunks(self, pcm, item_offset, item_samples, chunk_frames, max_item_samples=None):
+        """cac_get_end_run: for every recording of the flat CUDA float32 tensor `pcm` the index of the first
+        chunk of `chunk_frames` frames whose mel values are all equal, -1 if there is none; CUDA int32 [n], queued
+        on the current stream (tables: numpy / list, or CUDA int64 tensors together with max_item_samples)."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        off, ns, mx = _item_tables(pcm, item_offset, item_samples)
+        if max_item_samples is None:
+            assert mx is not None, "device item tables need max_item_samples"
+            max_item_samples = mx
+        n = int(off.numel())
+        out = torch.empty((n,), dtype=torch.int32, device=dev)
+        if n == 0:
+            return out
+        need = lib.cac_get_end_work_bytes(self._h, n, int(max_item_samples), int(chunk_frames))
+        work = _work_buffer(self, need, dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_get_end_run(self._h, pcm.data_ptr(), off.data_ptr(), ns.data_ptr(), n, int(max_item_samples),
+                                      int(chunk_frames), out.data_ptr(), work.data_ptr(), work.numel(), _stream_ptr(torch)))
+        return out
 
     def morepork_windows(self, spec, win_frame0, win_width, out=None):
         torch = _torch()
@@ -527,25 +567,37 @@ class pinned:
         return False
 
 
-def signal_components_queue(spec, dilate_h, dilate_w, erode_h, result):
-    """cac_signal_components_async: queue the chain for one recording; `result` is a CUDA int32 tensor of
-    4 + 6 * max_components values that receives [count, -, -, -, (min x, min y, max x, max y, area, order) ...]."""
+def _work_buffer(holder, need, dev):
+    """A 256-byte aligned CUDA scratch tensor of at least `need` bytes cached on `holder` (grown, never shrunk)."""
     torch = _torch()
-    assert spec.is_cuda and spec.dtype == torch.float32 and spec.is_contiguous() and spec.dim() == 2
-    assert result.is_cuda and result.dtype == torch.int32 and result.is_contiguous()
-    rows, cols = spec.shape
-    max_components = (result.numel() - 4) // 6
-    with torch.cuda.device(spec.device):
-        check(lib.cac_signal_components_async(spec.data_ptr(), rows, cols, int(dilate_h), int(dilate_w), int(erode_h),
-                                              int(max_components), result.data_ptr(), _stream_ptr(torch)))
+    buf = getattr(holder, "_work", None)
+    if buf is None or buf.numel() < need or buf.device != dev:
+        buf = torch.empty(int(need), dtype=torch.uint8, device=dev)      # torch allocations are 512-byte aligned
+        holder._work = buf
+    return buf
 
 
-def signal_components_collect(result_host):
-    """[count, ...] block (numpy int32, downloaded) -> [n, 6] = (x, y, width, height, area, order)."""
+def _item_tables(pcm, item_offset, item_samples):
+    """(offsets, lengths) as CUDA int64 tensors + the longest length; accepts numpy / lists (uploaded) or CUDA tensors."""
+    torch = _torch()
+    if hasattr(item_offset, "is_cuda") and item_offset.is_cuda:
+        assert item_samples.is_cuda and item_offset.dtype == item_samples.dtype == torch.int64
+        return item_offset, item_samples, None
+    off = np.ascontiguousarray(item_offset, dtype=np.int64)
+    ns = np.ascontiguousarray(item_samples, dtype=np.int64)
+    assert off.shape == ns.shape and off.ndim == 1
+    assert len(off) == 0 or ((off >= 0).all() and (ns >= 0).all() and int((off + ns).max()) <= pcm.numel())
+    both = torch.from_numpy(np.stack([off, ns])).to(pcm.device, non_blocking=True)
+    return both[0], both[1], (int(ns.max()) if len(ns) else 0)
+
+
+def collect_components(result_host):
+    """[count, -, -, -, (min x, min y, max x, max y, area, order) ...] block (numpy int32, downloaded) ->
+    [n, 6] = (x, y, width, height, area, order), cv2's stats layout + the label-order key."""
     count = int(result_host[0])
     max_components = (result_host.size - 4) // 6
     if count > max_components:
-        raise CacError("more connected components than max_components")
+        raise CacError("more connected components (%d) than max_components (%d)" % (count, max_components))
     raw = result_host[4:4 + 6 * count].reshape(count, 6)
     out = raw.copy()
     out[:, 2] = raw[:, 2] - raw[:, 0] + 1
@@ -553,18 +605,84 @@ def signal_components_collect(result_host):
     return out
 
 
+class SignalNoisePlan:
+    """cac_sn_*: signal_noise (src/identify_tracks.py:650-691) up to the connected-component table, for batches of
+    recordings on the device.  dilate_h / dilate_w / erode_h are the reference's height / width / height // 10."""
+
+    def __init__(self, hop_length, dilate_h, dilate_w, erode_h, device=0):
+        self.hop_length, self.device = int(hop_length), int(device)
+        self._h = _vp()
+        self._work = None
+        check(lib.cac_sn_plan_create(self.hop_length, int(dilate_h), int(dilate_w), int(erode_h), self.device,
+                                     ctypes.byref(self._h)))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.cac_sn_plan_destroy(self._h)
+            self._h = None
+
+    def frame_count(self, n_samples):
+        return int(lib.cac_sn_frame_count(self._h, int(n_samples)))
+
+    def run(self, pcm, item_offset, item_samples, max_components=4096, max_item_samples=None, result=None):
+        """Queue the whole chain for every recording pcm[off_i : off_i + n_i] of the flat CUDA float32 tensor `pcm`
+        (tables: numpy / list, or CUDA int64 tensors together with max_item_samples).  Returns the CUDA int32 tensor
+        [n, 4 + 6 * max_components]; nothing is synchronised."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
+        off, ns, mx = _item_tables(pcm, item_offset, item_samples)
+        if max_item_samples is None:
+            assert mx is not None, "device item tables need max_item_samples"
+            max_item_samples = mx
+        n = int(off.numel())
+        if result is None:
+            result = torch.empty((n, 4 + 6 * int(max_components)), dtype=torch.int32, device=dev)
+        assert result.is_cuda and result.dtype == torch.int32 and result.is_contiguous() and result.numel() >= n * (4 + 6 * int(max_components))
+        if n == 0:
+            return result
+        need = lib.cac_sn_work_bytes(self._h, n, int(max_item_samples))
+        work = _work_buffer(self, need, dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_sn_run(self._h, pcm.data_ptr(), off.data_ptr(), ns.data_ptr(), n, int(max_item_samples),
+                                 int(max_components), result.data_ptr(), work.data_ptr(), work.numel(), _stream_ptr(torch)))
+        return result
+
+    def spectrum(self, pcm):
+        """First stage for one recording (1-D CUDA float32 tensor): (|stft| [2049, cols] unscaled, column medians [cols],
+        a_max [1]) as CUDA tensors."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous() and pcm.dim() == 1
+        cols = self.frame_count(pcm.numel())
+        spec = torch.empty((2049, cols), dtype=torch.float32, device=dev)
+        colmed = torch.empty((cols,), dtype=torch.float32, device=dev)
+        amax = torch.zeros((1,), dtype=torch.float32, device=dev)
+        work = _work_buffer(self, 4096, dev)
+        with torch.cuda.device(dev):
+            check(lib.cac_sn_spectrum_run(self._h, pcm.data_ptr(), pcm.numel(), spec.data_ptr(), colmed.data_ptr(),
+                                          amax.data_ptr(), work.data_ptr(), work.numel(), _stream_ptr(torch)))
+        return spec, colmed, amax
+
+
+class _ComponentsScratch:
+    _work = None
+
+
 def signal_components(spec, dilate_h, dilate_w, erode_h, max_components=65536, want_masks=False):
-    """cac_signal_components on a CUDA float32 [rows, cols] normalised spectrogram: returns the int32
+    """cac_signal_components_run on a CUDA float32 [rows, cols] normalised spectrogram: returns the int32
     numpy array [n, 6] = (x, y, width, height, area, order) (and the three stage masks if asked)."""
     torch = _torch()
     assert spec.is_cuda and spec.dtype == torch.float32 and spec.is_contiguous() and spec.dim() == 2
     rows, cols = spec.shape
-    stats = np.empty((max_components, 6), dtype=np.int32)
-    count = ctypes.c_int32(0)
+    result = torch.empty((4 + 6 * int(max_components),), dtype=torch.int32, device=spec.device)
     masks = torch.empty((3, rows, cols), dtype=torch.uint8, device=spec.device) if want_masks else None
+    need = lib.cac_signal_components_work_bytes(rows, cols)
+    work = _work_buffer(_ComponentsScratch, need, spec.device)
     with torch.cuda.device(spec.device):
-        check(lib.cac_signal_components(spec.data_ptr(), rows, cols, int(dilate_h), int(dilate_w), int(erode_h),
-                                        int(max_components), stats.ctypes.data_as(_vp), ctypes.byref(count),
-                                        masks.data_ptr() if want_masks else None, _stream_ptr(torch)))
-    stats = stats[:count.value].copy()
+        check(lib.cac_signal_components_run(spec.data_ptr(), rows, cols, int(dilate_h), int(dilate_w), int(erode_h),
+                                            int(max_components), result.data_ptr(),
+                                            masks.data_ptr() if want_masks else None, work.data_ptr(), work.numel(),
+                                            _stream_ptr(torch)))
+    stats = collect_components(result.cpu().numpy())
     return (stats, masks) if want_masks else stats

@@ -12,18 +12,7 @@ import numpy as np
 from . import custommel
 
 
-class Signal:
-    """Track record with the attributes load_samples reads (src/identify_tracks.py:915-986)."""
-
-    def __init__(self, start, end, freq_start, freq_end):
-        self.start = start
-        self.end = end
-        self.freq_start = freq_start
-        self.freq_end = freq_end
-
-    @property
-    def length(self):
-        return self.end - self.start
+from .tracks import Signal, get_tracks_from_signals, merge_signals  # noqa: F401  (src/identify_tracks.py:725-842, 915-1033)
 
 
 @functools.lru_cache(maxsize=16)
@@ -218,47 +207,71 @@ def _get_end_plan(sr, device=0):
     return engine.SpecPlan(n_fft, 281, n_mels=120, power=1, mel_weights=w, device=device)
 
 
+def _as_batch(recordings, device):
+    """list of 1-D arrays / CUDA tensors, or a 2-D array / tensor [n, samples] -> (flat CUDA float32 tensor,
+    offsets, lengths) without copying what is already one contiguous CUDA block."""
+    import torch
+    dev = torch.device("cuda", device)
+    if hasattr(recordings, "dim") and recordings.dim() == 2 and recordings.is_cuda and recordings.is_contiguous() \
+            and recordings.dtype == torch.float32:
+        n, m = recordings.shape
+        return recordings.reshape(-1), np.arange(n, dtype=np.int64) * m, np.full(n, m, dtype=np.int64)
+    items = [recordings[i] for i in range(len(recordings))]
+    lens = np.array([int(r.shape[0]) for r in items], dtype=np.int64)
+    if len(items) == 1 and _is_cuda(items[0]) and items[0].dtype == torch.float32 and items[0].is_contiguous():
+        return items[0].reshape(-1), np.zeros(1, np.int64), lens              # one uploaded recording: used in place
+    padded = (lens + 3) // 4 * 4                                   # keep every recording 16-byte aligned
+    offs = np.concatenate([[0], np.cumsum(padded)[:-1]]).astype(np.int64) if len(items) else np.zeros(0, np.int64)
+    flat = torch.zeros((int(padded.sum()),), dtype=torch.float32, device=dev)
+    for r, o, n in zip(items, offs, lens):
+        src = r if _is_cuda(r) else torch.from_numpy(np.ascontiguousarray(r, dtype=np.float32))
+        flat[o:o + n].copy_(src, non_blocking=True)
+    return flat, offs, lens
+
+
+def get_end_batch(recordings, sr):
+    """get_end (src/identify_tracks.py:387-413) for many recordings with one launch chain and one synchronisation:
+    `recordings` as for signal_noise_batch.  STFT (n_fft = sr // 10, hop 281), the 120-mel projection and the
+    1-second chunk scan all run on the device (cac_get_end_run); returns one value per recording, equal to get_end()."""
+    hop_length = 281
+    plan = _get_end_plan(int(sr))
+    flat, offs, lens = _as_batch(recordings, plan.device)
+    if len(lens) == 0:
+        return []
+    chunk_length = sr // hop_length
+    first = plan.get_end_chunks(flat, offs, lens, chunk_length).cpu().numpy()          # the one synchronisation
+    return [int(c) * chunk_length * hop_length // sr if c >= 0 else int(n) / sr for c, n in zip(first.tolist(), lens.tolist())]
+
+
 def get_end(frames, sr):
     """src/identify_tracks.py:387-413: first 1-second chunk of the 120-mel magnitude spectrogram
     (n_fft = sr // 10, hop 281) whose values are all equal (digital silence) -> its start in whole
-    seconds; else the file length.  STFT, mel and the per-chunk min/max run on the GPU.
+    seconds; else the file length.  STFT, mel and the chunk scan run on the GPU (one recording of get_end_batch).
     `frames`: numpy array or the CUDA tensor to_device() returned."""
-    from . import engine
-    hop_length = 281
     plan = _get_end_plan(int(sr))
-    dev_frames = to_device(frames, plan.device)
-    mel, base = plan.run(dev_frames, [0], [frames.shape[0]])
-    n_frames = int(base[-1])
-    chunk_length = sr // hop_length
-    mm = engine.chunk_minmax(mel.view(120, n_frames), chunk_length).cpu().numpy()
-    start = 0
-    end = start + chunk_length
-    file_length = len(frames) / sr
-    while end < n_frames:
-        lo, hi = mm[start // chunk_length]
-        if hi == lo:
-            return start * hop_length // sr
-        start = end
-        end = start + chunk_length
-    return file_length
+    return get_end_batch([to_device(frames, plan.device)], sr)[0]
 
 
-@functools.lru_cache(maxsize=4)
-def _signal_noise_plan(hop_length, device=0):
+@functools.lru_cache(maxsize=8)
+def _signal_noise_plan(sr, hop_length, device=0):
+    """Structuring elements as signal_noise derives them (src/identify_tracks.py:673-684): width = int(0.25 sr / hop),
+    height = index of the first FFT bin above 100 Hz, plus one."""
     from . import engine
-    return engine.SpecPlan(4096, hop_length, bin_lo=0, bin_hi=2049, n_mels=0, power=1, bin_major=True, device=device)
+    width = int(SIGNAL_WIDTH * sr / hop_length)
+    freqs = np.fft.rfftfreq(n=4096, d=1.0 / sr)                  # librosa.fft_frequencies
+    above = np.nonzero(freqs > 100)[0]
+    height = int(above[0]) + 1 if len(above) else 0
+    plan = engine.SignalNoisePlan(hop_length, height, width, height // 10, device=device)
+    plan.width, plan.height, plan.freqs = width, height, freqs
+    return plan
 
 
 def signal_noise_spectrogram(frames, sr, hop_length=281):
     """First stage of signal_noise (src/identify_tracks.py:650-657): |STFT(n_fft=4096, hop)| of the
-    whole recording divided by its maximum, as a CUDA float32 tensor [2049, n_frames] that stays on
-    the device for the median / morphology stages."""
-    import torch
-    from . import engine
-    plan = _signal_noise_plan(int(hop_length))
-    spec, base, a_max = plan.run(to_device(frames, plan.device), [0], [frames.shape[0]], want_max=True)
-    engine.scale_by_max(spec, a_max)
-    return spec.view(2049, int(base[-1]))
+    whole recording divided by its maximum, as a CUDA float32 tensor [2049, n_frames]."""
+    plan = _signal_noise_plan(int(sr), int(hop_length))
+    spec, _, a_max = plan.spectrum(to_device(frames, plan.device))
+    return spec.div_(a_max)                                       # IEEE float32 division, as numpy's
 
 
 SIGNAL_WIDTH = 0.25   # src/identify_tracks.py:21
@@ -281,47 +294,109 @@ def _signals_from_stats(stats, sr, width, height, freqs, signal_cls):
 
 
 def signal_noise_batch(recordings, sr, hop_length=281, signal_cls=None, max_components=4096):
-    """signal_noise (src/identify_tracks.py:650-706) for MANY recordings with one synchronisation: `recordings` is a list
-    of 1-D numpy arrays / CUDA tensors or a 2-D array / tensor [n, samples].  Per recording the spectrum, its maximum,
-    the scaling and the median / mask / morphology / component chain (cac_signal_components_async) are queued on the
-    current stream; the small component tables come back together at the end.  Returns one list of Signal per
-    recording, equal to signal_noise() called on each."""
-    import torch
-    from . import engine
-    n_fft = 4096
-    plan = _signal_noise_plan(int(hop_length))
-    width = int(SIGNAL_WIDTH * sr / hop_length)
-    freqs = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)
-    above = np.nonzero(freqs > 100)[0]
-    height = int(above[0]) + 1 if len(above) else 0
-    items = [recordings[i] for i in range(len(recordings))]
-    if not items:
+    """signal_noise (src/identify_tracks.py:650-706) for MANY recordings: `recordings` is a list of 1-D numpy arrays /
+    CUDA tensors or a 2-D array / CUDA tensor [n, samples].  One cac_sn_run call queues the whole chain for all of them
+    (spectrum with column medians, row medians + threshold mask, morphology, connected components; recordings go on
+    the grid, nothing is launched per recording), the small component tables come back with one copy.  A recording
+    with more than max_components components (pathological noise) is redone alone with room for 65,536.  Returns
+    one list of Signal per recording, equal to signal_noise() called on each."""
+    plan = _signal_noise_plan(int(sr), int(hop_length))
+    flat, offs, lens = _as_batch(recordings, plan.device)
+    if len(lens) == 0:
         return []
-    dev = torch.device("cuda", plan.device)
-    results = torch.empty((len(items), 4 + 6 * max_components), dtype=torch.int32, device=dev)
-    for i, rec in enumerate(items):
-        frames = to_device(rec, plan.device)
-        spec, base, a_max = plan.run(frames, [0], [frames.shape[0]], want_max=True)
-        engine.scale_by_max(spec, a_max)
-        engine.signal_components_queue(spec.view(2049, int(base[-1])), height, width, height // 10, results[i])
-    host = results.cpu().numpy()                                  # the one synchronisation
-    return [_signals_from_stats(engine.signal_components_collect(host[i]), sr, width, height, freqs, signal_cls)
-            for i in range(len(items))]
+    from . import engine
+    host = plan.run(flat, offs, lens, max_components=max_components).cpu().numpy()     # the one synchronisation
+    out = []
+    for i in range(len(lens)):
+        if int(host[i, 0]) > max_components:
+            row = plan.run(flat, offs[i:i + 1], lens[i:i + 1], max_components=65536).cpu().numpy()[0]
+        else:
+            row = host[i]
+        out.append(_signals_from_stats(engine.collect_components(row), sr, plan.width, plan.height, plan.freqs, signal_cls))
+    return out
 
 
 def signal_noise(frames, sr, hop_length=281, signal_cls=None):
     """src/identify_tracks.py:650-706: candidate track signals of a recording (`signal_cls`: the class to
-    build, e.g. the reference's own Signal with its merge helpers; default: this module's Signal).  STFT magnitude,
-    medians, threshold, morphology and connected components run on the GPU
-    (signal_noise_spectrogram + engine.signal_components); the handful of component boxes comes back
-    to the host, where the reference's filter (:689-691) and time / frequency conversion (:697-704,
-    including its hard-coded 281) are applied.  Returns a list of Signal."""
+    build, e.g. tracks.Signal with the reference's merge helpers; default: this module's Signal).  STFT magnitude,
+    medians, threshold, morphology and connected components run on the GPU (one recording of signal_noise_batch);
+    the handful of component boxes comes back to the host, where the reference's filter (:689-691) and time /
+    frequency conversion (:697-704, including its hard-coded 281) are applied.  Returns a list of Signal.
+    Supported range: any sr whose structuring element height (first FFT bin above 100 Hz, + 1) is at most 255
+    (sr >= 1.7 kHz; erode height 0, sr > ~51 kHz, behaves like cv2's empty kernel) and recordings of up to
+    2^31 / 2049 frames (~100 minutes at hop 281 / 48 kHz)."""
+    plan = _signal_noise_plan(int(sr), int(hop_length))
+    return signal_noise_batch([to_device(frames, plan.device)], sr, hop_length, signal_cls, max_components=65536)[0]
+
+
+def classify_prep_batch(recordings, sr, segment_length=3, segment_stride=1.5, hop_length=281, mean_sub=False,
+                        mel_break=1000, htk=True, n_mels=160, fmin=50, fmax=11000, channels=1, power=2, db_scale=False,
+                        normalize=True, n_fft=4096, pad_short_tracks=False, max_components=4096, want_samples=True):
+    """Everything classify does to a recording before its model runs (src/identify_tracks.py:416-440, 502-524) for a
+    batch of decoded recordings, with TWO synchronisations in total:
+      1. get_end -> signal_noise(frames[: int(sr * length)]) chained on the device (the trimmed lengths are computed on
+         the GPU from get_end's chunk index and handed to cac_sn_run as its device item table), one copy brings back
+         the end chunks and the component tables of all recordings;
+      2. the host turns components into signals and tracks (get_tracks_from_signals, O(100) boxes per recording), and
+         ONE cac_features_run produces the classifier segments of every track of every recording on the device.
+    Returns one dict per recording: tracks, length, signals (copies taken before the merge, as classify keeps them for
+    the chirp count), raw_length, and samples = one CUDA tensor [n_segments, n_mels, frames, channels] per track
+    (what load_samples_device returns; None when want_samples is False).  Consumes np.random like load_samples."""
+    import torch
     from . import engine
-    n_fft = 4096
-    spec = signal_noise_spectrogram(frames, sr, hop_length)
-    width = int(SIGNAL_WIDTH * sr / hop_length)
-    freqs = np.fft.rfftfreq(n=n_fft, d=1.0 / sr)                  # librosa.fft_frequencies
-    above = np.nonzero(freqs > 100)[0]
-    height = int(above[0]) + 1 if len(above) else 0
-    stats = engine.signal_components(spec, height, width, height // 10)
-    return _signals_from_stats(stats, sr, width, height, freqs, signal_cls)
+    sn = _signal_noise_plan(int(sr), 281)                         # classify passes 281 (:420)
+    ge = _get_end_plan(int(sr))
+    flat, offs, lens = _as_batch(recordings, sn.device)
+    n = len(lens)
+    if n == 0:
+        return []
+    dev = flat.device
+    chunk_length = sr // 281
+    max_len = int(lens.max())
+    tables = torch.from_numpy(np.stack([offs, lens, np.array([int(sr * (int(m) / sr)) for m in lens], dtype=np.int64)])).to(dev)
+    first = ge.get_end_chunks(flat, tables[0], tables[1], chunk_length, max_item_samples=max_len)
+    # frames[: int(sr * length)] with length = chunk * chunk_length * 281 // sr whole seconds, or len / sr (:387-420)
+    first64 = first.to(torch.int64)
+    secs = torch.div(first64 * (chunk_length * 281), sr, rounding_mode="floor")
+    trimmed = torch.minimum(torch.where(first64 >= 0, secs * sr, tables[2]), tables[1])
+    comp = sn.run(flat, tables[0], trimmed, max_components=max_components, max_item_samples=max_len)
+    first_h = first.cpu().numpy()                                  # synchronisation 1 (both results are ready)
+    comp_h = comp.cpu().numpy()
+    out, all_segs, per_rec = [], [], []
+    feat_kw = dict(fmin=fmin, fmax=fmax, pad_short_tracks=pad_short_tracks)
+    for i in range(n):
+        c = int(first_h[i])
+        length = c * chunk_length * 281 // sr if c >= 0 else int(lens[i]) / sr
+        row = comp_h[i]
+        if int(row[0]) > max_components:                           # pathological recording: redo it alone
+            n_trim = int(sr * length)
+            row = sn.run(flat, offs[i:i + 1], np.array([min(n_trim, int(lens[i]))]), max_components=65536).cpu().numpy()[0]
+        signals = _signals_from_stats(engine.collect_components(row), sr, sn.width, sn.height, sn.freqs, Signal)
+        tracks = get_tracks_from_signals([s.copy() for s in signals], length)
+        rec = {"tracks": tracks, "length": length, "signals": signals, "raw_length": int(lens[i]) / sr, "samples": None}
+        if want_samples and tracks:
+            segs, counts = segment_descriptors(int(lens[i]), sr, tracks, segment_length, segment_stride, **feat_kw)
+            segs["pcm_offset"] += int(offs[i])
+            all_segs.append(segs)
+            per_rec.append((i, counts))
+        out.append(rec)
+    if want_samples and all_segs:
+        if not htk:
+            fmin, fmax, power, mel_break = 50, 11000, 2, None
+        plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break, int(sr * segment_length),
+                     int(power), bool(db_scale), bool(normalize))
+        segs = np.concatenate(all_segs)
+        block = engine.spect_tail(plan.run(flat, segs), mean_sub, channels)
+        k = 0
+        for i, counts in per_rec:
+            samples = []
+            for cnt in counts:
+                samples.append(block[k:k + cnt])
+                k += cnt
+            out[i]["samples"] = samples
+    return out
+
+
+def classify_prep(frames, sr, **kw):
+    """classify_prep_batch for one recording: one upload, two synchronisations (see there)."""
+    return classify_prep_batch([to_device(frames)], sr, **kw)[0]

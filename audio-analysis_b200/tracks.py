@@ -1,0 +1,171 @@
+"""Host half of track finding: the `Signal` record and the interval-merge heuristics that turn signal_noise's
+component boxes into tracks (src/identify_tracks.py:709-842, 915-1033).  O(100) rectangles per recording and pure
+scalar logic, so it stays on the host; it is here so that the GPU stages on either side of it
+(signal_noise before, load_samples after) form one drop-in chain.  Results are pinned against the reference's own
+functions on seeded rectangles (tests/golden/tracks.npz, tests/test_tracks_host.py).
+"""
+import numpy as np
+
+
+def segment_overlap(first, second):
+    """Overlap of two (lo, hi) intervals, negative = size of the gap (src/identify_tracks.py:709-714)."""
+    return (first[1] - first[0]) + (second[1] - second[0]) - (max(first[1], second[1]) - min(first[0], second[0]))
+
+
+def mel_freq(f):
+    """HTK mel (src/identify_tracks.py:717-718)."""
+    return 2595.0 * np.log10(1.0 + f / 700.0)
+
+
+class Signal:
+    """src/identify_tracks.py:915-1033: a time / frequency box plus the classifier's verdict on it.  Compared and
+    removed by identity, like the reference's class (no __eq__)."""
+
+    def __init__(self, start, end, freq_start, freq_end):
+        self.start = start
+        self.end = end
+        self.freq_start = freq_start
+        self.freq_end = freq_end
+        self._refresh_mel()
+        self.results = []
+        self.master_tag = None
+        self.master_model = None
+        self.master_below_thresh = True
+        self.track_id = None
+
+    def _refresh_mel(self):
+        self.mel_freq_start = mel_freq(self.freq_start)
+        self.mel_freq_end = mel_freq(self.freq_end)
+
+    # -- geometry ------------------------------------------------------------------------------------------
+    @property
+    def length(self):
+        return self.end - self.start
+
+    @property
+    def freq_range(self):
+        return self.freq_end - self.freq_start
+
+    @property
+    def mel_freq_range(self):
+        return self.mel_freq_end - self.mel_freq_start
+
+    def time_overlap(self, other):
+        return segment_overlap((self.start, self.end), (other.start, other.end))
+
+    def freq_overlap(self, other):
+        return segment_overlap((self.freq_start, self.freq_end), (other.freq_start, other.freq_end))
+
+    def mel_freq_overlap(self, other):
+        return segment_overlap((self.mel_freq_start, self.mel_freq_end), (other.mel_freq_start, other.mel_freq_end))
+
+    def copy(self):
+        return Signal(self.start, self.end, self.freq_start, self.freq_end)
+
+    def to_array(self, decimals=1):
+        box = [self.start, self.end, self.freq_start, self.freq_end]
+        return box if decimals is None else list(np.round(np.array(box), decimals))
+
+    def merge(self, other):
+        """Bounding box of both (:1004-1010)."""
+        self.start, self.end = min(self.start, other.start), max(self.end, other.end)
+        self.freq_start, self.freq_end = min(self.freq_start, other.freq_start), max(self.freq_end, other.freq_end)
+        self._refresh_mel()
+
+    def enlarge(self, scale, min_track_length):
+        """Grow around the centre in time (at least min_track_length, clipped at 0) and frequency, the latter
+        truncated to ints (:985-1002)."""
+        grow_t = (max(self.length * scale, min_track_length) - self.length) / 2
+        self.start = max(self.start - grow_t, 0)
+        self.end = self.end + grow_t
+        grow_f = (self.freq_range * scale - self.freq_range) / 2
+        lo = self.freq_start - grow_f
+        self.freq_end = int(self.freq_end + grow_f)
+        self.freq_start = int(max(lo, 0))
+        self._refresh_mel()
+
+    # -- metadata ------------------------------------------------------------------------------------------
+    def get_meta(self):
+        """The per-track entry of analysis_result["species_identify"] (:1015-1033)."""
+        meta = {"begin_s": self.start, "end_s": self.end, "freq_start": self.freq_start, "freq_end": self.freq_end}
+        if self.master_tag is not None:
+            meta["master_tag"] = {"below_thresh": self.master_below_thresh, "prediction": self.master_tag.get_meta(),
+                                  "model": self.master_model}
+        meta["model_results"] = [r.get_meta() for r in self.results]
+        if self.track_id is not None:
+            meta["track_id"] = self.track_id
+        return meta
+
+    def __str__(self):
+        return f"Signal: {self.start}-{self.end} f: {self.freq_start}-{self.freq_end}"
+
+
+def _should_merge(s, u):
+    """The three merge rules of one (s, u) pair (src/identify_tracks.py:745-785); None = the pair is skipped."""
+    same_side = (u.mel_freq_end < 1500 and s.mel_freq_end < 1500) or (u.mel_freq_end > 1500 and s.mel_freq_end > 1500)
+    if not same_side:
+        return False
+    t_overlap = s.time_overlap(u)
+    need = 0.5 if (s.mel_freq_start > 1000 and u.mel_freq_start > 1000) else 0.75
+    gap = s.start - u.end if s.start > u.end else u.start - s.end
+    m_overlap = s.mel_freq_overlap(u)
+    if t_overlap > u.length * 0.75 and m_overlap > -20:
+        return True
+    if t_overlap > 0 and m_overlap > u.mel_freq_range * need:
+        return True
+    if m_overlap > u.mel_freq_range * need and gap <= 2:
+        if u.mel_freq_end > s.mel_freq_range:
+            similar = s.mel_freq_range / u.mel_freq_range
+        else:
+            similar = u.mel_freq_range / s.mel_freq_range
+        return similar >= 0.75
+    return False
+
+
+def merge_signals(signals):
+    """One merging sweep (src/identify_tracks.py:725-792): signals ordered by start (ties: highest mel_freq_end first);
+    each surviving signal absorbs the FIRST other survivor it may merge with.  Returns (signals, anything merged)."""
+    ordered = sorted(sorted(signals, key=lambda s: s.mel_freq_end, reverse=True), key=lambda s: s.start)
+    dead = []
+    gone = lambda x: any(x is d for d in dead)
+    for s in ordered:
+        if gone(s):
+            continue
+        for u in ordered:
+            if u is s or gone(u):
+                continue
+            if _should_merge(s, u):
+                s.merge(u)
+                dead.append(u)
+                break
+    survivors = [s for s in ordered if not gone(s)]
+    return survivors, bool(dead)
+
+
+def get_tracks_from_signals(signals, end):
+    """src/identify_tracks.py:795-842: merge until nothing merges, drop short signals, enlarge the rest by 1.4x (at
+    least 0.7 s, clipped to [0, end]) absorbing signals that overlap more than 70 % of the shorter one, drop tracks
+    narrower than 50 mel.  Quirk kept: the minimum length starts at 0.35 s but is overwritten by every overlap test
+    with the shorter length of the pair just compared (:803, :826)."""
+    merged = True
+    while merged:
+        signals, merged = merge_signals(signals)
+    dead = []
+    gone = lambda x: any(x is d for d in dead)
+    min_length = 0.35
+    for s in signals:
+        if gone(s):
+            continue
+        if s.length < min_length:
+            dead.append(s)
+            continue
+        s.enlarge(1.4, min_track_length=0.7)
+        s.end = min(end, s.end)
+        for other in signals:
+            if other is s or gone(other):
+                continue
+            min_length = min(s.length, other.length)
+            if s.time_overlap(other) > 0.7 * min_length:
+                s.merge(other)
+                dead.append(other)
+    return [s for s in signals if not gone(s) and not s.mel_freq_range < 50]

@@ -11,7 +11,12 @@
  * for the calling thread's last failure is cac_last_error().  Pointers named d_* are device
  * pointers owned by the caller (e.g. torch tensors' data_ptr()), h_* are host pointers.
  * `stream` is a cudaStream_t passed as void* (NULL = default stream).  *_run functions do
- * not allocate or synchronise; *_host functions copy in, run, copy out and synchronise.
+ * not allocate or synchronise (cac_spec_run, cac_ci_run, cac_ci_entries_run, cac_morepork_windows_run and
+ * cac_resample_run take small HOST offset tables and stage them with one cudaMemcpyAsync into a plan-owned
+ * buffer that grows on demand; the cac_sn_* and cac_get_end_* entry points take device tables and never
+ * touch the host); *_host functions copy in, run, copy out and synchronise.  cac_features_run cannot
+ * validate device-side segment descriptors: out-of-range descriptors are the caller's responsibility
+ * (cac_features_host checks them).
  * There is no CPU fallback anywhere behind this interface.
  */
 #ifndef CACOPHONY_B200_H
@@ -79,6 +84,12 @@ int cac_plan_frames(const cac_plan* plan);
  * waits for that kernel and returns its duration. */
 int cac_plan_set_profiling(cac_plan* plan, int enable);
 int cac_plan_last_kernel_ms(cac_plan* plan, float* ms);
+/* MagTransform.call (src/magtransform.py:17-19, src/magtransformv2.py:19-21: y = x ** sigmoid(a), the first layer
+ * of models whose metadata sets db_scale False, selected by `magv2` at src/identify_tracks.py:313-316) as an epilogue
+ * of the fused kernel: with it enabled cac_features_run / cac_features_host write mel ** sigmoid(a) directly - one
+ * powf per value in the kernel's flush instead of another read and write of the whole output (cac_magtransform_run).
+ * Only for plans with db_scale = 0 that the fused kernel serves (n_fft 4096, bands below bin 1024). */
+int cac_plan_set_magtransform(cac_plan* plan, int enable, float a);
 /* Bytes of device scratch cac_features_run needs for n_segments (the unfused path adds the normalised segment rows). */
 size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
 
@@ -186,6 +197,17 @@ int cac_scale_by_max_run(float* d_data, int64_t n, const float* d_max, void* str
 /* get_end's chunk scan (src/identify_tracks.py:404-412): d_out[c] = {min, max} of
  * d_in[:, c*chunk : (c+1)*chunk] for the n_cols // chunk complete chunks of a row-major [n_rows][n_cols] matrix. */
 int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int32_t chunk, float* d_out, void* stream);
+/* identify_tracks.get_end (src/identify_tracks.py:387-413) for n_items recordings with one launch chain and no host
+ * round trip: `plan` is the n_fft = sr // 10, hop 281, 120-mel, power 1 plan get_end uses (:389-399); recording i =
+ * d_pcm[d_item_offset[i] .. + d_item_samples[i]) (DEVICE arrays; lengths above max_item_samples are clamped).  The
+ * mel values never reach HBM: the kernel's epilogue keeps each chunk's extrema (chunk_frames = sr // 281 frames,
+ * :404) and a scan kernel applies the reference's loop (:406-412).  d_out[i] = index of the first chunk whose maximum
+ * equals its minimum (the caller returns chunk * chunk_frames * 281 // sr seconds), or -1 (return len / sr).
+ * d_work: cac_get_end_work_bytes(...) bytes, 256-byte aligned.  Neither allocates nor synchronises. */
+size_t cac_get_end_work_bytes(const cac_spec_plan* plan, int64_t n_items, int64_t max_item_samples, int32_t chunk_frames);
+int cac_get_end_run(cac_spec_plan* plan, const float* d_pcm, const int64_t* d_item_offset, const int64_t* d_item_samples,
+                    int64_t n_items, int64_t max_item_samples, int32_t chunk_frames, int32_t* d_out, void* d_work,
+                    size_t work_bytes, void* stream);
 /* identify_morepork's window loop body (src/identify_morepork.py:150-166): window w covers
  * h_win_width[w] (<= 60) frames of the frame-major raw spectrum d_spec starting at global frame
  * h_win_frame0[w]; librosa.amplitude_to_db(ref=np.max), rescale by |min|, zero-pad to 60 columns;
@@ -193,25 +215,47 @@ int cac_chunk_minmax_run(const float* d_in, int32_t n_rows, int64_t n_cols, int3
 int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec, const int64_t* h_win_frame0,
                              const int32_t* h_win_width, int64_t n_windows, float* d_out, void* stream);
 
-/* signal_noise after its STFT (src/identify_tracks.py:658-691) on the normalised magnitude spectrogram
- * d_spec [rows][cols] (rows = FFT bins, cols = frames; what cac_spec_run + cac_scale_by_max_run leave on
- * the device): np.median along both axes, signal = (spec > 3 col_median) & (spec > 3 row_median),
- * cv2.morphologyEx(MORPH_OPEN, ones((4,4))), cv2.dilate(ones((dilate_h, dilate_w))),
- * cv2.erode(ones((erode_h, dilate_w))), cv2.connectedComponentsWithStats (8-connected).
- * h_stats[i] = {x, y, width, height, area, order} for the *h_count components (background excluded);
- * `order` sorts components like cv2's labels (first 2x2 block in raster order).  d_stage_masks (may
- * be NULL) receives the three uint8 [rows][cols] masks (threshold, opened, closed).  Synchronous; allocates
- * and frees its own scratch. */
-int cac_signal_components(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
-                          int32_t erode_h, int32_t max_components, int32_t* h_stats, int32_t* h_count,
-                          uint8_t* d_stage_masks, void* stream);
-
-/* The same chain queued on `stream` without the read-back, for batches (one call per recording, one synchronisation
- * for all): d_result receives 4 + 6 * max_components int32 - [0] = number of components (the call's results are
+/* ---- signal_noise (src/identify_tracks.py:650-691) for batches of recordings --------------------------------------
+ * |librosa.stft(frames, n_fft=4096, hop_length)| (:652-654), a_max (:656), np.median along both axes of spectogram / a_max
+ * (:657-659), signal = (spec > 3 col_median) & (spec > 3 row_median) (:667), cv2.morphologyEx(MORPH_OPEN, ones((4, 4)))
+ * (:669-671), cv2.dilate(ones((dilate_h, dilate_w))), cv2.erode(ones((erode_h, dilate_w))) (:683-684; erode_h == 0 is
+ * cv2's empty kernel = its 3 x 3 default) and cv2.connectedComponentsWithStats (8-connected, :686) - everything up to
+ * the component table.  dilate_h = `height`, dilate_w = `width`, erode_h = height // 10 as derived at :673-684
+ * (audio-analysis_b200/identify_tracks.py computes them from sr and hop).  The matrix is written to HBM once and read
+ * once: column medians are selected by the warp that transformed the frame, row medians and the threshold mask by the
+ * CTA that holds the row in registers, both on the unscaled magnitudes (division by a_max is monotone, the selected
+ * values are scaled afterwards - bit-identical to the reference's order of operations).  Recordings are processed in
+ * waves of as many as fit the work buffer; no launch, allocation, copy or synchronisation per recording. */
+typedef struct cac_sn_plan cac_sn_plan;
+int cac_sn_plan_create(int32_t hop_length, int32_t dilate_h, int32_t dilate_w, int32_t erode_h, int device,
+                       cac_sn_plan** out);
+int cac_sn_plan_destroy(cac_sn_plan* plan);
+/* columns of the spectrogram: 1 + n_samples // hop_length (librosa.stft, centre = True) */
+int64_t cac_sn_frame_count(const cac_sn_plan* plan, int64_t n_samples);
+/* recommended size of d_work for n_items recordings of at most max_item_samples samples (24 wave slots of
+ * 4 * 2049 * frames + ~8 MB each; any size that holds one slot works, cac_sn_run just takes more waves) */
+size_t cac_sn_work_bytes(const cac_sn_plan* plan, int64_t n_items, int64_t max_item_samples);
+/* Recording i = d_pcm[d_item_offset[i] .. + d_item_samples[i]) - DEVICE arrays (a length above max_item_samples is
+ * clamped to it).  d_result[i] = 4 + 6 * max_components int32: [0] = number of components (the recording's table is
  * invalid if it exceeds max_components), then from [4] per component {min x, min y, max x, max y, area, order}
- * (width = max x - min x + 1, height likewise).  Scratch is allocated and freed in stream order. */
-int cac_signal_components_async(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
-                                int32_t erode_h, int32_t max_components, int32_t* d_result, void* stream);
+ * (cv2's stats: x, y, width = max x - min x + 1, height likewise, area); `order` sorts the components like cv2's
+ * labels (first 2 x 2 block in raster order).  d_work: 256-byte aligned.  Neither allocates nor synchronises. */
+int cac_sn_run(cac_sn_plan* plan, const float* d_pcm, const int64_t* d_item_offset, const int64_t* d_item_samples,
+               int64_t n_items, int64_t max_item_samples, int32_t max_components, int32_t* d_result, void* d_work,
+               size_t work_bytes, void* stream);
+/* The first stage alone for one recording (:652-656): d_spec [2049][cols] = |stft| (not yet divided by its maximum),
+ * d_colmed [cols] = np.median(|stft|, axis=0), *d_amax = np.amax(|stft|).  d_work: 512 bytes, 256-byte aligned. */
+int cac_sn_spectrum_run(cac_sn_plan* plan, const float* d_pcm, int64_t n_samples, float* d_spec, float* d_colmed,
+                        float* d_amax, void* d_work, size_t work_bytes, void* stream);
+
+/* The stages after the STFT (:658-686) on a spectrogram the caller supplies: d_spec [rows][cols] = spectogram / a_max.
+ * Same kernels as cac_sn_run behind the column medians (taken through a transpose here).  d_result as above for one
+ * recording; d_stage_masks (may be NULL) receives the three uint8 [rows][cols] masks (threshold, opened, closed).
+ * d_work: cac_signal_components_work_bytes(rows, cols) bytes, 256-byte aligned.  Neither allocates nor synchronises. */
+size_t cac_signal_components_work_bytes(int32_t rows, int64_t cols);
+int cac_signal_components_run(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
+                              int32_t erode_h, int32_t max_components, int32_t* d_result, uint8_t* d_stage_masks,
+                              void* d_work, size_t work_bytes, void* stream);
 
 /* Rational-rate resampling front-end: replaces `ffmpeg -ar 16000` in front of the Cacophony
  * Index (src/common.py:76-79) and librosa.resample to 48 kHz (src/identify_tracks.py:55-57).  The filter is the

@@ -61,7 +61,7 @@ def test_signal_noise_equals_reference_fixture(engine, golden, name, seed, secon
 def test_threshold_mask_differs_only_near_thresholds(engine):
     from audio_analysis_b200 import identify_tracks as T
     rec = synth.recording(1234, seconds=12.0)
-    spec = T.signal_noise_spectrogram(rec, 48000)
+    spec = T.signal_noise_spectrogram(rec, 48000).contiguous()
     _, masks = engine.signal_components(spec, 10, 42, 1, want_masks=True)
     ref_spec = O.signal_noise_spectrogram(rec, 48000)
     _, mask, _, _, _ = O.signal_noise_stages(rec, 48000)
@@ -99,7 +99,7 @@ def test_frames_uploaded_once_give_the_same_results(engine):
 
 
 def test_signal_noise_batch_equals_per_recording_calls(engine):
-    """signal_noise_batch queues every recording's chain (cac_signal_components_async) and synchronises once."""
+    """signal_noise_batch: one cac_sn_run call for all recordings (ragged lengths), one synchronisation."""
     import time
     import torch
     from audio_analysis_b200 import identify_tracks as T
@@ -109,11 +109,75 @@ def test_signal_noise_batch_equals_per_recording_calls(engine):
     batch = T.signal_noise_batch(recs, 48000)
     assert [key(b) for b in batch] == single
     assert T.signal_noise_batch([], 48000) == []
-    # throughput note (printed with -s): 16 one-minute recordings already on the device
-    pool = torch.from_numpy(synth.batch(500, 16, seconds=60.0)).cuda()
-    T.signal_noise_batch(pool[:2], 48000)
+    # throughput note (printed with -s): 32 one-minute recordings already on the device (two waves of 24 slots)
+    pool = torch.from_numpy(synth.batch(500, 32, seconds=60.0)).cuda()
+    T.signal_noise_batch(pool[:2].contiguous(), 48000)
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
     out = T.signal_noise_batch(pool, 48000)
     dt = time.perf_counter() - t0
-    print("signal_noise_batch: %.3f ms per one-minute recording (16 per call)" % (dt / 16 * 1e3))
-    assert len(out) == 16 and key(out[3]) == key(T.signal_noise(pool[3], 48000))
+    print("signal_noise_batch: %.3f ms per one-minute recording (32 per call)" % (dt / 32 * 1e3))
+    assert len(out) == 32
+    for i in (3, 23, 24, 31):                                      # both waves, first and last slots
+        assert key(out[i]) == key(T.signal_noise(pool[i], 48000))
+
+
+def test_spectrum_stage_medians_and_maximum_are_exact(engine):
+    """cac_sn_spectrum_run: the column medians selected inside the spectrum kernel equal np.median of the matrix the
+    same kernel wrote, a_max equals its maximum, and the matrix matches the oracle's float64 STFT."""
+    from audio_analysis_b200 import identify_tracks as T
+    for seed, seconds in ((1234, 12.0), (5, 1.3), (6, 0.05)):
+        rec = synth.recording(seed, seconds=seconds)
+        plan = T._signal_noise_plan(48000, 281)
+        spec, colmed, amax = plan.spectrum(T.to_device(rec))
+        spec, colmed, amax = spec.cpu().numpy(), colmed.cpu().numpy(), float(amax.cpu().numpy()[0])
+        assert spec.shape == (2049, 1 + len(rec) // 281)
+        assert np.array_equal(colmed, np.median(spec, axis=0))
+        assert amax == spec.max()
+        ref = O.signal_noise_spectrogram(rec, 48000)               # normalised by its own maximum
+        assert np.abs(spec / np.float32(amax) - ref).max() <= 2e-6
+
+
+def test_batch_chain_equals_standalone_chain_on_its_own_spectrum(engine):
+    """cac_sn_run (medians from inside the kernels, unscaled matrix) == cac_signal_components_run fed
+    spectrum / a_max (the reference's order of operations), component for component."""
+    import torch
+    from audio_analysis_b200 import identify_tracks as T
+    rec = synth.recording(99, seconds=14.0)
+    plan = T._signal_noise_plan(48000, 281)
+    dev = T.to_device(rec)
+    got = engine.collect_components(plan.run(dev, [0], [len(rec)], max_components=4096).cpu().numpy()[0])
+    spec = T.signal_noise_spectrogram(dev, 48000)
+    ref = engine.signal_components(spec, plan.height, plan.width, plan.height // 10)
+    srt = lambda a: a[np.argsort(a[:, 5], kind="stable")]
+    assert len(got) == len(ref) and np.array_equal(srt(got), srt(ref))
+
+
+def test_component_overflow_falls_back_per_recording(engine):
+    """A recording with more components than max_components is redone alone; the others of the batch are kept."""
+    from audio_analysis_b200 import identify_tracks as T
+    recs = [synth.recording(70, seconds=8.0), synth.recording(71, seconds=11.5)]
+    key = lambda sigs: [(s.start, s.end, s.freq_start, s.freq_end) for s in sigs]
+    full = T.signal_noise_batch(recs, 48000)
+    tiny = T.signal_noise_batch(recs, 48000, max_components=1)
+    assert [key(a) for a in tiny] == [key(b) for b in full]
+
+
+def test_other_sample_rates_follow_cv2(engine):
+    """sr = 16 kHz: height 27 -> erode (2, 13); sr = 96 kHz: height 6 -> erode height 0 = cv2's empty kernel (3 x 3)."""
+    from audio_analysis_b200 import identify_tracks as T
+    for sr in (16000, 96000):
+        rec = synth.recording(12, seconds=6.0, sr=sr)
+        ref = O.signal_noise(rec, sr)                             # [(start, end, freq_start, freq_end)]
+        got = T.signal_noise(rec, sr)
+        assert [(s.start, s.end, s.freq_start, s.freq_end) for s in got] == [tuple(r) for r in ref]
+
+
+def test_get_end_batch_equals_get_end(engine):
+    from audio_analysis_b200 import identify_tracks as T
+    recs = [synth.recording(31, seconds=9.0, zero_tail_s=2.0), synth.recording(32, seconds=7.5),
+            synth.recording(33, seconds=12.0, zero_tail_s=5.5), np.zeros(48000 * 3, np.float32)]
+    want = [O.get_end(r, 48000) for r in recs]
+    assert T.get_end_batch(recs, 48000) == want
+    assert [T.get_end(r, 48000) for r in recs] == want
+    assert T.get_end_batch([], 48000) == []
