@@ -126,29 +126,64 @@ def calculate(source_file_name, loader=None):
 
 
 class Stream:
-    """Long-form recordings fed in chunks (BASELINE.json configs[3]): the carried state is the
-    tail of samples from the last finished window on (that window is recomputed to seed
-    previous_bins) plus the points so far.  feed() accepts numpy float32 chunks of any size;
-    result() returns exactly what calculate() returns on the concatenation."""
+    """Long-form recordings fed in chunks (BASELINE.json configs[3]): the carried state is the tail of samples from
+    the last finished window on (that window is recomputed to seed previous_bins) plus the points so far.  feed()
+    accepts chunks of any size - numpy float32 arrays, page-locked torch CPU tensors (uploaded as they are) or CUDA
+    tensors; result() returns exactly what calculate() returns on the concatenation.
+    The carry lives on the DEVICE and nothing synchronises before result(): a chunk goes up on a copy stream (numpy
+    chunks through two alternating page-locked staging buffers) while the kernels of the previous chunk run."""
 
     def __init__(self, device=0):
         import torch
         self._torch = torch
         self.plan = _plan(WINDOW_SIZE, SAMPLE_RATE, device)
         self.device = device
-        self._carry = numpy.zeros(0, numpy.float32)
+        self._carry = None             # device tensor: samples from _carry_start on
         self._carry_start = 0          # absolute sample index of _carry[0]
         self._next_window = 0          # index of the next window to compute (offset 1024 * (w + 1))
         self._total = 0
         self._points = []              # CUDA uint8 tensors
+        self._copy_stream = None       # created with the first upload
+        self._stage = [None, None]     # page-locked staging buffers for pageable chunks
+        self._stage_done = [None, None]
+        self._k = 0
 
-    def _upload(self, seg):
-        return self._torch.from_numpy(seg).cuda(self.device)
+    def _upload(self, chunk):
+        """chunk -> CUDA float32 tensor, the copy queued on the copy stream; the compute stream waits for it."""
+        torch = self._torch
+        device = torch.device("cuda", self.device)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=device)
+        if hasattr(chunk, "is_cuda") and chunk.is_cuda:
+            return chunk.to(device, torch.float32).reshape(-1)
+        if isinstance(chunk, numpy.ndarray):
+            chunk = numpy.ascontiguousarray(chunk, dtype=numpy.float32).reshape(-1)
+            k = self._k
+            self._k ^= 1
+            if self._stage_done[k] is not None:
+                self._stage_done[k].synchronize()              # the copy that last used this staging buffer is done
+            if self._stage[k] is None or self._stage[k].numel() < chunk.shape[0]:
+                self._stage[k] = torch.empty(chunk.shape[0], dtype=torch.float32).pin_memory()
+            src = self._stage[k][:chunk.shape[0]]
+            src.numpy()[:] = chunk
+        else:
+            src, k = chunk.reshape(-1), None                   # torch CPU tensor (page-locked: truly asynchronous)
+        cur = torch.cuda.current_stream(device)
+        with torch.cuda.stream(self._copy_stream):
+            dev = src.to(device, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(self._copy_stream)
+        if k is not None:
+            self._stage_done[k] = done
+        cur.wait_event(done)
+        dev.record_stream(cur)
+        return dev
 
     def feed(self, chunk):
-        chunk = numpy.ascontiguousarray(chunk, dtype=numpy.float32)
-        buf = numpy.concatenate([self._carry, chunk]) if self._carry.size else chunk
-        self._total += chunk.shape[0]
+        torch = self._torch
+        dev_chunk = self._upload(chunk)
+        buf = torch.cat([self._carry, dev_chunk]) if self._carry is not None and self._carry.numel() else dev_chunk
+        self._total += int(dev_chunk.numel())
         n_final = self.plan.window_count(self._total)          # windows that exist whatever follows
         if n_final <= self._next_window:
             self._carry = buf
@@ -160,15 +195,13 @@ class Stream:
         n_new = n_final - w0
         n_samples = 1024 * (n_new + 2) + 2048                  # window_count(n_samples) == n_new
         assert self.plan.window_count(n_samples) == n_new
-        seg = buf[start:start + n_samples]
-        if seg.shape[0] < n_samples:                           # only padding beyond the last window's end
-            seg = numpy.concatenate([seg, numpy.zeros(n_samples - seg.shape[0], numpy.float32)])
-        pcm = self._upload(seg)
-        _, points, _ = self.plan.run(pcm, [0], [n_samples])
+        if start + n_samples > buf.numel():                    # only padding beyond the last window's end
+            buf = torch.cat([buf, torch.zeros(start + n_samples - buf.numel(), dtype=torch.float32, device=buf.device)])
+        _, points, _ = self.plan.run(buf, [start], [n_samples])
         self._points.append(points[1:])                        # points[0] = 255: window w0 only seeds previous_bins
         self._next_window = n_final
         keep_from = 1024 * (n_final - 1) - self._carry_start   # next pseudo-recording starts at window n_final - 1
-        self._carry = buf[keep_from:].copy()
+        self._carry = buf[keep_from:self._total - self._carry_start].clone()
         self._carry_start += keep_from
 
     def result(self):

@@ -19,14 +19,15 @@ struct SnItem {                                // one recording of the wave, wri
     int wpr;                                   // mask words per row = (cols + 31) / 32
     int stage_base;                            // first stage (frames_per_stage consecutive frames) within the wave
     int n_stages;
-    int pad;
+    int pitch;                                 // floats per row of the recording's matrix (cols rounded up to 32; cols
+                                               // itself when the caller supplies the matrix)
 };
 
 struct SnWave {                                // by-value kernel argument
     const SnItem* items;
     int n_items;
     int rows;                                  // 2049 for the fused chain; any for cac_signal_components_run
-    float* spec;        long long spec_stride;     // [rows][cols] float32 magnitudes (unscaled), floats per slot
+    float* spec;        long long spec_stride;     // [rows][pitch] float32 magnitudes (unscaled), floats per slot
     float* colmed;      long long col_stride;      // [cols] column medians (unscaled)
     float* colthr;                                 // [cols] fl(3 * fl(colmed / a_max)), same stride
     unsigned* amax;                                // [n_items] max magnitude (float bits)

@@ -11,8 +11,8 @@
 using namespace cac;
 
 namespace cac {
-__global__ void sn_single_item_kernel(SnItem* items, unsigned* amax, long long pcm_off, int n_samples, int cols, int fps,
-                                      unsigned amax_bits) {
+__global__ void sn_single_item_kernel(SnItem* items, unsigned* amax, long long pcm_off, int n_samples, int cols, int pitch,
+                                      int fps, unsigned amax_bits) {
     SnItem im;
     im.pcm_off = pcm_off;
     im.n_samples = n_samples;
@@ -20,7 +20,7 @@ __global__ void sn_single_item_kernel(SnItem* items, unsigned* amax, long long p
     im.wpr = (cols + 31) / 32;
     im.stage_base = 0;
     im.n_stages = (cols + fps - 1) / fps;
-    im.pad = 0;
+    im.pitch = pitch;
     items[0] = im;
     amax[0] = amax_bits;
 }
@@ -51,7 +51,7 @@ Layout layout(int rows, long long max_cols, int slots) {
     L.col_stride = (size_t)(max_cols + 31) / 32 * 32;
     L.plane_stride = (size_t)rows * L.max_wpr;
     L.bits_stride = 3 * L.plane_stride;
-    L.spec_stride = ((size_t)rows * max_cols + 63) / 64 * 64;
+    L.spec_stride = (size_t)rows * (size_t)((max_cols + 31) / 32 * 32);   // rows of the matrix are padded to 32 floats
     size_t o = 0;
     L.items = o; o += up((size_t)slots * sizeof(SnItem));
     L.amax = o; o += up((size_t)slots * sizeof(unsigned));
@@ -198,7 +198,7 @@ extern "C" int cac_sn_spectrum_run(cac_sn_plan* plan, const float* d_pcm, int64_
     w.spec = d_spec;
     w.colmed = d_colmed;
     w.amax = reinterpret_cast<unsigned*>(d_amax);
-    sn_single_item_kernel<<<1, 1, 0, st>>>(items, w.amax, 0, (int)n_samples, (int)cols, plan->fps, 0u);
+    sn_single_item_kernel<<<1, 1, 0, st>>>(items, w.amax, 0, (int)n_samples, (int)cols, (int)((cols + 31) / 32 * 32), plan->fps, 0u);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(launch_sn_stft(d_pcm, w, plan->hop, plan->fps, st));
     return CAC_OK;
@@ -227,7 +227,7 @@ extern "C" int cac_signal_components_run(const float* d_spec, int32_t rows, int6
     SnWave w = wave_of(L, (char*)d_work, rows, 1, d_result, 4 + 6LL * max_components, max_components);
     float* scratch = w.spec;                              // transposed copy now, label forest later
     w.spec = const_cast<float*>(d_spec);                  // read-only for every kernel of this path
-    sn_single_item_kernel<<<1, 1, 0, st>>>(const_cast<SnItem*>(w.items), w.amax, 0, 0, (int)cols, 1, 0x3f800000u /* 1.0f */);
+    sn_single_item_kernel<<<1, 1, 0, st>>>(const_cast<SnItem*>(w.items), w.amax, 0, 0, (int)cols, (int)cols, 1, 0x3f800000u /* 1.0f */);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(launch_transpose(d_spec, scratch, rows, cols, st));
     CUDA_TRY(launch_row_median(scratch, w.colmed, cols, rows, st));

@@ -3,7 +3,8 @@
 //   row_medians = np.median(spectogram, axis=1)
 //   signal = (spectogram > 3 * column_medians) & (spectogram > 3 * row_medians)
 // One CTA per (row, recording).  The row is read from HBM ONCE into registers; the median is selected there by a
-// four-pass 8-bit radix select on the unscaled values (division by a_max is monotone: the order statistic of the
+// radix select on the unscaled values (sn_select.cuh: below the common prefix of the row's smallest and largest key,
+// 12 bits per pass - two passes for a typical row; division by a_max is monotone, so the order statistic of the
 // quotients is the quotient of the order statistic), the one or two selected values are scaled, and the mask of the
 // row is formed on the spot from fl(x / a_max) - bit-identical to the reference's arithmetic - and written bit-packed
 // (32 cells per ballot).  The scaled matrix, the transposed matrix and the separate mask pass of the first version
@@ -25,68 +26,103 @@ __global__ void __launch_bounds__(256) sn_col_thresholds_kernel(const SnWave w) 
     w.colthr[o] = __fmul_rn(3.0f, __fdiv_rn(w.colmed[o], a));
 }
 
-// shared tail: median of the scaled row from the selected order statistics, then the row's mask words.
+struct RowSel {                       // shared scratch of one CTA's select
+    unsigned hist[kSelCtaBins];
+    unsigned tot[32];
+    unsigned out[2];
+    unsigned mn, mx, cnt_le, min_gt;
+};
+
+// CTA-wide minimum / maximum of per-thread values (all threads call; ends with a barrier)
+template <int NT>
+__device__ __forceinline__ void cta_minmax(RowSel& s, unsigned mn, unsigned mx) {
+    if (threadIdx.x == 0) { s.mn = 0xffffffffu; s.mx = 0u; }
+    __syncthreads();
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) { atomicMin(&s.mn, mn); atomicMax(&s.mx, mx); }
+    __syncthreads();
+}
+
+// median of the SCALED row from the selected order statistic(s): v1 = rank (cols - 1) / 2 of the unscaled keys,
+// cnt_le / min_gt = how many keys are <= v1 and the smallest key above it (only read for an even count)
+__device__ __forceinline__ float scaled_median(unsigned v1, unsigned cnt_le, unsigned min_gt, int cols, float a) {
+    float med = __fdiv_rn(__uint_as_float(v1), a);
+    if ((cols & 1) == 0) {
+        // even count: the next order statistic is v1 again when enough elements are <= v1, else the smallest one above;
+        // np.median -> np.mean of the two middle float32 values
+        const unsigned k0 = (unsigned)((cols - 1) / 2);
+        const unsigned v2 = (cnt_le >= k0 + 2u) ? v1 : min_gt;
+        med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);
+    }
+    return med;
+}
+
 // NT threads hold PER keys each, element i of thread t = column t + NT i (a warp's 32 lanes = one mask word).
 template <int NT, int PER>
 __global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
-    __shared__ __align__(16) unsigned hist[kSelHistWords];
-    __shared__ unsigned s_prefix, s_k, s_cnt_le, s_min_gt;
+    __shared__ __align__(16) RowSel s;
     const int item = blockIdx.y, row = blockIdx.x;
     const SnItem im = w.items[item];
     const int cols = im.cols;
     if (cols > NT * PER) return;                            // served by a wider instantiation (launch_sn_rowmed_mask)
     const int tid = threadIdx.x, lane = tid & 31;
-    const unsigned* rowp = reinterpret_cast<const unsigned*>(w.spec + (size_t)item * w.spec_stride) + (size_t)row * cols;
+    const unsigned* rowp = reinterpret_cast<const unsigned*>(w.spec + (size_t)item * w.spec_stride) + (size_t)row * im.pitch;
     unsigned key[PER];
+    unsigned mn = 0xffffffffu, mx = 0u;
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const int c = tid + NT * i;
-        key[i] = c < cols ? __ldg(rowp + c) : 0xffffffffu;
+        key[i] = c < cols ? __ldg(rowp + c) : 0u;
     }
-    const unsigned k0 = (unsigned)((cols - 1) / 2);
-    unsigned prefix = 0u, k = k0;
-    unsigned* hl = hist + (lane & 3);
-#pragma unroll 1
-    for (int pass = 3; pass >= 0; --pass) {
-        const int shift = 8 * pass;
-        const unsigned himask = pass == 3 ? 0u : (0xffffffffu << (shift + 8));
-        for (int i = tid; i < kSelHistWords; i += NT) hist[i] = 0u;
-        __syncthreads();
 #pragma unroll
-        for (int i = 0; i < PER; ++i)
-            if (tid + NT * i < cols && (key[i] & himask) == prefix) atomicAdd(hl + ((key[i] >> shift) & 255u) * 4, 1u);
-        __syncthreads();
-        if (tid < 32) {
-            unsigned kk = k;
-            const unsigned digit = sel_scan_digit(hist, lane, kk);
-            if (lane == 0) { s_prefix = prefix | (digit << shift); s_k = kk; }
+    for (int i = 0; i < PER; ++i)
+        if (tid + NT * i < cols) { mn = min(mn, key[i]); mx = max(mx, key[i]); }
+    cta_minmax<NT>(s, mn, mx);
+    mn = s.mn;
+    mx = s.mx;
+    const unsigned k0 = (unsigned)((cols - 1) / 2);
+    unsigned v1 = mx;
+    if (mn != mx) {                                         // uniform for the CTA
+        int remaining = 32 - __clz(mn ^ mx);                // bits [0, remaining) vary
+        unsigned prefix = remaining >= 32 ? 0u : (mx >> remaining) << remaining;
+        unsigned k = k0;
+#pragma unroll 1
+        while (remaining > 0) {
+            const int wd = min(kSelCtaBits, remaining), shift = remaining - wd;
+            const unsigned dmask = (1u << wd) - 1u;
+            const unsigned above = remaining >= 32 ? 0u : 0xffffffffu << remaining;   // bits fixed so far
+            uint4* h4 = reinterpret_cast<uint4*>(s.hist);
+            for (int i = tid; i < kSelCtaBins / 4; i += NT) h4[i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < PER; ++i)
+                smem_inc_if(s.hist + ((key[i] >> shift) & dmask), tid + NT * i < cols && ((key[i] ^ prefix) & above) == 0u);
+            __syncthreads();
+            sel_scan_cta<NT>(s.hist, k, s.tot, s.out);
+            prefix |= s.out[0] << shift;
+            k = s.out[1];
+            remaining = shift;
+            __syncthreads();                                // s.out is read before the next pass rewrites it
         }
-        __syncthreads();
-        prefix = s_prefix;
-        k = s_k;
+        v1 = prefix;
     }
-    const unsigned v1 = prefix;
-    const float a = __uint_as_float(w.amax[item]);
-    float med = __fdiv_rn(__uint_as_float(v1), a);
     if ((cols & 1) == 0) {
-        // even count: the next order statistic is v1 again when enough elements are <= v1, else the smallest one above
-        if (tid == 0) { s_cnt_le = 0u; s_min_gt = 0xffffffffu; }
+        if (tid == 0) { s.cnt_le = 0u; s.min_gt = 0xffffffffu; }
         __syncthreads();
-        unsigned cnt = 0u, mn = 0xffffffffu;
+        unsigned cnt = 0u, gt = 0xffffffffu;
 #pragma unroll
         for (int i = 0; i < PER; ++i)
             if (tid + NT * i < cols) {
-                if (key[i] <= v1) ++cnt; else mn = min(mn, key[i]);
+                if (key[i] <= v1) ++cnt; else gt = min(gt, key[i]);
             }
         cnt = __reduce_add_sync(0xffffffffu, cnt);
-        mn = __reduce_min_sync(0xffffffffu, mn);
-        if (lane == 0) { atomicAdd(&s_cnt_le, cnt); atomicMin(&s_min_gt, mn); }
+        gt = __reduce_min_sync(0xffffffffu, gt);
+        if (lane == 0) { atomicAdd(&s.cnt_le, cnt); atomicMin(&s.min_gt, gt); }
         __syncthreads();
-        const unsigned v2 = (s_cnt_le >= k0 + 2u) ? v1 : s_min_gt;
-        // np.median -> np.mean of the two middle float32 values (of the SCALED row)
-        med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);
     }
-    const float tr = __fmul_rn(3.0f, med);
+    const float a = __uint_as_float(w.amax[item]);
+    const float tr = __fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a));
     const float* thr = w.colthr + (size_t)item * w.col_stride;
     unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
 #pragma unroll
@@ -102,61 +138,66 @@ __global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
     }
 }
 
-// Rows longer than the register-resident variants cover (recordings of more than ~2.4 minutes at hop 281):
+// Rows longer than the register-resident variants cover (recordings of more than ~4 minutes at hop 281):
 // the same select with the row re-read from global memory (L2) in every pass.
 __global__ void __launch_bounds__(256) sn_rowmed_mask_long_kernel(const SnWave w) {
-    __shared__ __align__(16) unsigned hist[kSelHistWords];
-    __shared__ unsigned s_prefix, s_k, s_cnt_le, s_min_gt;
+    constexpr int NT = 256;
+    __shared__ __align__(16) RowSel s;
     const int item = blockIdx.y, row = blockIdx.x;
     const SnItem im = w.items[item];
     const int cols = im.cols;
     if (cols <= kSnMaxColsFast) return;
     const int tid = threadIdx.x, lane = tid & 31;
-    const unsigned* rowp = reinterpret_cast<const unsigned*>(w.spec + (size_t)item * w.spec_stride) + (size_t)row * cols;
+    const unsigned* rowp = reinterpret_cast<const unsigned*>(w.spec + (size_t)item * w.spec_stride) + (size_t)row * im.pitch;
+    unsigned mn = 0xffffffffu, mx = 0u;
+    for (int c = tid; c < cols; c += NT) { const unsigned key = rowp[c]; mn = min(mn, key); mx = max(mx, key); }
+    cta_minmax<NT>(s, mn, mx);
+    mn = s.mn;
+    mx = s.mx;
     const unsigned k0 = (unsigned)((cols - 1) / 2);
-    unsigned prefix = 0u, k = k0;
-    unsigned* hl = hist + (lane & 3);
-    for (int pass = 3; pass >= 0; --pass) {
-        const int shift = 8 * pass;
-        const unsigned himask = pass == 3 ? 0u : (0xffffffffu << (shift + 8));
-        for (int i = tid; i < kSelHistWords; i += 256) hist[i] = 0u;
-        __syncthreads();
-        for (int c = tid; c < cols; c += 256) {
-            const unsigned key = rowp[c];
-            if ((key & himask) == prefix) atomicAdd(hl + ((key >> shift) & 255u) * 4, 1u);
+    unsigned v1 = mx;
+    if (mn != mx) {
+        int remaining = 32 - __clz(mn ^ mx);
+        unsigned prefix = remaining >= 32 ? 0u : (mx >> remaining) << remaining;
+        unsigned k = k0;
+        while (remaining > 0) {
+            const int wd = min(kSelCtaBits, remaining), shift = remaining - wd;
+            const unsigned dmask = (1u << wd) - 1u;
+            const unsigned above = remaining >= 32 ? 0u : 0xffffffffu << remaining;
+            uint4* h4 = reinterpret_cast<uint4*>(s.hist);
+            for (int i = tid; i < kSelCtaBins / 4; i += NT) h4[i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+            for (int c = tid; c < cols; c += NT) {
+                const unsigned key = rowp[c];
+                smem_inc_if(s.hist + ((key >> shift) & dmask), ((key ^ prefix) & above) == 0u);
+            }
+            __syncthreads();
+            sel_scan_cta<NT>(s.hist, k, s.tot, s.out);
+            prefix |= s.out[0] << shift;
+            k = s.out[1];
+            remaining = shift;
+            __syncthreads();
         }
-        __syncthreads();
-        if (tid < 32) {
-            unsigned kk = k;
-            const unsigned digit = sel_scan_digit(hist, lane, kk);
-            if (lane == 0) { s_prefix = prefix | (digit << shift); s_k = kk; }
-        }
-        __syncthreads();
-        prefix = s_prefix;
-        k = s_k;
+        v1 = prefix;
     }
-    const unsigned v1 = prefix;
-    const float a = __uint_as_float(w.amax[item]);
-    float med = __fdiv_rn(__uint_as_float(v1), a);
     if ((cols & 1) == 0) {
-        if (tid == 0) { s_cnt_le = 0u; s_min_gt = 0xffffffffu; }
+        if (tid == 0) { s.cnt_le = 0u; s.min_gt = 0xffffffffu; }
         __syncthreads();
-        unsigned cnt = 0u, mn = 0xffffffffu;
-        for (int c = tid; c < cols; c += 256) {
+        unsigned cnt = 0u, gt = 0xffffffffu;
+        for (int c = tid; c < cols; c += NT) {
             const unsigned key = rowp[c];
-            if (key <= v1) ++cnt; else mn = min(mn, key);
+            if (key <= v1) ++cnt; else gt = min(gt, key);
         }
         cnt = __reduce_add_sync(0xffffffffu, cnt);
-        mn = __reduce_min_sync(0xffffffffu, mn);
-        if (lane == 0) { atomicAdd(&s_cnt_le, cnt); atomicMin(&s_min_gt, mn); }
+        gt = __reduce_min_sync(0xffffffffu, gt);
+        if (lane == 0) { atomicAdd(&s.cnt_le, cnt); atomicMin(&s.min_gt, gt); }
         __syncthreads();
-        const unsigned v2 = (s_cnt_le >= k0 + 2u) ? v1 : s_min_gt;
-        med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);
     }
-    const float tr = __fmul_rn(3.0f, med);
+    const float a = __uint_as_float(w.amax[item]);
+    const float tr = __fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a));
     const float* thr = w.colthr + (size_t)item * w.col_stride;
     unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
-    for (int c0 = 0; c0 < cols; c0 += 256) {                // uniform trip count: every lane reaches the ballot
+    for (int c0 = 0; c0 < cols; c0 += NT) {                 // uniform trip count: every lane reaches the ballot
         const int c = c0 + tid;
         bool on = false;
         if (c < cols) {
@@ -181,7 +222,7 @@ cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, cudaStream_t st
     if (max_cols <= 256 * 8) sn_rowmed_mask_kernel<256, 8><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 16) sn_rowmed_mask_kernel<256, 16><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 32) sn_rowmed_mask_kernel<256, 32><<<grid, 256, 0, st>>>(w);
-    else if (max_cols <= 256 * 48) sn_rowmed_mask_kernel<256, 48><<<grid, 256, 0, st>>>(w);
+    else if (max_cols <= 256 * 44) sn_rowmed_mask_kernel<256, 44><<<grid, 256, 0, st>>>(w);   // one-minute recordings: 10,250
     else {
         sn_rowmed_mask_kernel<512, 48><<<grid, 512, 0, st>>>(w);         // rows up to 24,576 columns
         if (max_cols > kSnMaxColsFast) sn_rowmed_mask_long_kernel<<<grid, 256, 0, st>>>(w);   // the longer ones

@@ -7,12 +7,17 @@
 //
 // Same structure as stft_mel_kernel: persistent, one CTA of 12 warps per SM, work unit = a stage of
 // frames_per_stage consecutive frames of one recording, samples of stage q + 1 arrive by cp.async while stage q is
-// transformed, one warp per frame (fft4096.cuh).  The warp that transformed a frame still holds its 2,049
-// magnitudes: it stores them bin-major (one float per row of the recording's matrix; the 12 warps of the CTA
-// work on consecutive frames, L2 merges the sectors), and selects their median by a four-pass radix select whose
-// histogram reuses the warp's exchange buffer - no transpose, no second matrix, no extra pass over HBM.
+// transformed, one warp per frame (fft4096.cuh).  The 12 warps of the CTA work on 12 consecutive frames; their
+// buffers together are a [12][2049] tile that the CTA writes bin-major as contiguous 48-byte runs (rows of the
+// matrix are padded to a pitch of 32 floats, so the runs are 16-byte aligned: full sectors, no partial-sector
+// read-modify-write in L2 / HBM - per-lane 4-byte stores had cost 1.75x the bytes and 40 % of the kernel).  The warp
+// that transformed a frame still holds its 2,049 magnitudes in registers and selects their median by a radix
+// select whose histogram reuses the warp's buffer - no transpose, no second matrix, no extra pass over HBM.
 #include "cac_common.cuh"
 #include "fft4096.cuh"
+#if CAC_FFT_PACKED
+#include "fft4096p.cuh"
+#endif
 #include "sn.cuh"
 #include "sn_select.cuh"
 
@@ -30,28 +35,34 @@ __host__ __device__ inline SnStftSmem sn_stft_layout(int stage_half) {
     return L;
 }
 
-// median (rank 1024 of the 2,049 magnitudes of one frame): lane holds bins lane + 32 i in v[], lane 0 also bin 2048
-__device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], float nyq, unsigned* hist, int lane) {
-    unsigned prefix = 0u, k = 1024u;
+// median (rank 1024 of the 2,049 magnitudes of one frame): lane holds bins lane + 32 i in v[], lane 0 also bin 2048;
+// mn / mx = smallest / largest of the 2,049 keys (warp-uniform).  Radix select below their common prefix, 11 bits per pass.
+__device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], float nyq, unsigned mn, unsigned mx,
+                                                      unsigned* hist, int lane) {
+    if (mn == mx) return mx;
+    const int top = 32 - __clz(mn ^ mx);                  // bits [0, top) vary; keys are < 2^31, so top <= 31
+    unsigned prefix = (mx >> top) << top;
+    unsigned k = 1024u;
     uint4* h4 = reinterpret_cast<uint4*>(hist);
-    unsigned* hl = hist + (lane & 3);
     const unsigned ekey = __float_as_uint(nyq);
+    int remaining = top;
 #pragma unroll 1
-    for (int pass = 3; pass >= 0; --pass) {
-        const int shift = 8 * pass;
-        const unsigned himask = pass == 3 ? 0u : (0xffffffffu << (shift + 8));
+    while (remaining > 0) {
+        const int w = min(kSelWarpBits, remaining), shift = remaining - w;
+        const unsigned dmask = (1u << w) - 1u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) h4[lane + 32 * j] = make_uint4(0u, 0u, 0u, 0u);
+        for (int j = 0; j < kSelWarpBins / 4 / 32; ++j) h4[lane + 32 * j] = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
             const unsigned key = __float_as_uint(v[i]);
-            if ((key & himask) == prefix) atomicAdd(hl + ((key >> shift) & 255u) * 4, 1u);
+            smem_inc_if(hist + ((key >> shift) & dmask), ((key ^ prefix) >> remaining) == 0u);
         }
-        if (lane == 0 && (ekey & himask) == prefix) atomicAdd(hl + ((ekey >> shift) & 255u) * 4, 1u);
+        smem_inc_if(hist + ((ekey >> shift) & dmask), lane == 0 && ((ekey ^ prefix) >> remaining) == 0u);
         __syncwarp();
-        const unsigned digit = sel_scan_digit(hist, lane, k);
+        const unsigned digit = sel_scan_warp(hist, lane, k);
         prefix |= digit << shift;
+        remaining = shift;
         __syncwarp();                                   // every lane has read the histogram before it is cleared again
     }
     return prefix;
@@ -120,30 +131,59 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
 
         float* spec = w.spec + (size_t)item * w.spec_stride;
         float* colmed = w.colmed + (size_t)item * w.col_stride;
-        const size_t rstep = (size_t)32 * im.cols;
         float vmax = 0.f;
+        // rounds of 12 consecutive frames, one per warp: transform, then the CTA writes each bin's 12 values as ONE
+        // contiguous 48-byte run (the 12 warps' buffers together are a [12][2049] tile), then every warp selects its
+        // frame's median with its buffer as the histogram
 #pragma unroll 1
-        for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
-            fft_frame<1, 32, true>(se, so, fi * hop, ex, pbuf, lane, lt);
-            __syncwarp();                      // lane 0's bin 2048 is visible
+        for (int r0 = 0; r0 < nfs; r0 += kWarpsPerCta) {
+            const int fi = r0 + warp;
+            const bool active = fi < nfs;
             float v[64];
+            float nyq = 0.f;
+            if (active) {
+#if CAC_FFT_PACKED
+                fft_frame_p<1, 32, true>(se, so, fi * hop, ex, pbuf, lane, lt);
+#else
+                fft_frame<1, 32, true>(se, so, fi * hop, ex, pbuf, lane, lt);
+#endif
+                __syncwarp();                  // lane 0's bin 2048 is visible
 #pragma unroll
-            for (int i = 0; i < 64; ++i) v[i] = pbuf[lane + 32 * i];     // the lane's own values, 2 |X[k]|
-            const float nyq = pbuf[2048];
-            __syncwarp();                      // the buffer is free: it becomes the histogram
-            float m = nyq;
+                for (int i = 0; i < 64; ++i) v[i] = pbuf[lane + 32 * i];     // the lane's own values, 2 |X[k]|
+                nyq = pbuf[2048];
+            }
+            __syncthreads();                   // the round's magnitudes are complete in the 12 buffers
+            {
+                const int nr = min(kWarpsPerCta, nfs - r0);
+                const float* tile = smem + L.ex;                          // frame j of the round: tile[j * kExFloats + bin]
+                float* orow = spec + (size_t)tid * im.pitch + (f0 + r0);
+                const size_t ostep = (size_t)(kWarpsPerCta * 32) * im.pitch;
+                if (nr == kWarpsPerCta) {      // f0 + r0 is a multiple of 4 and the pitch of 32: 16-byte aligned runs
+                    for (int bin = tid; bin < kSnRows; bin += kWarpsPerCta * 32, orow += ostep) {
+                        float4* o4 = reinterpret_cast<float4*>(orow);
 #pragma unroll
-            for (int i = 0; i < 64; ++i) m = fmaxf(m, v[i]);
-            vmax = fmaxf(vmax, m);
-            const int f = f0 + fi;
-            float* o = spec + (size_t)lane * im.cols + f;
+                        for (int q = 0; q < kWarpsPerCta / 4; ++q) {
+                            const float* t = tile + (4 * q) * kExFloats + bin;
+                            o4[q] = make_float4(0.5f * t[0], 0.5f * t[kExFloats], 0.5f * t[2 * kExFloats], 0.5f * t[3 * kExFloats]);
+                        }
+                    }
+                } else {
+                    for (int bin = tid; bin < kSnRows; bin += kWarpsPerCta * 32, orow += ostep)
+                        for (int j = 0; j < nr; ++j) orow[j] = 0.5f * tile[j * kExFloats + bin];
+                }
+            }
+            __syncthreads();                   // the buffers are free: they become the histograms
+            if (active) {
+                float mx = nyq, mn = nyq;
 #pragma unroll
-            for (int i = 0; i < 64; ++i, o += rstep) *o = 0.5f * v[i];
-            if (lane == 0) spec[(size_t)2048 * im.cols + f] = 0.5f * nyq;
-            const unsigned med = frame_median_bits(v, nyq, hist, lane);
-            if (lane == 0) colmed[f] = 0.5f * __uint_as_float(med);
+                for (int i = 0; i < 64; ++i) { mx = fmaxf(mx, v[i]); mn = fminf(mn, v[i]); }
+                mx = warp_max(mx);
+                mn = warp_min(mn);
+                vmax = fmaxf(vmax, mx);
+                const unsigned med = frame_median_bits(v, nyq, __float_as_uint(mn), __float_as_uint(mx), hist, lane);
+                if (lane == 0) colmed[f0 + fi] = 0.5f * __uint_as_float(med);
+            }
         }
-        vmax = warp_max(vmax);
         if (lane == 0) atomicMax(w.amax + item, __float_as_uint(0.5f * vmax));
         if (last_of_item) { ++item; sidx = 0; } else ++sidx;
     }
@@ -162,7 +202,7 @@ __global__ void sn_prep_kernel(const long long* __restrict__ off, const long lon
             im.wpr = (im.cols + 31) / 32;
             im.stage_base = base;
             im.n_stages = (im.cols + fps - 1) / fps;
-            im.pad = 0;
+            im.pitch = (im.cols + 31) / 32 * 32;
             base += im.n_stages;
             items[i] = im;
         }

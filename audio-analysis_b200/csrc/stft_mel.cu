@@ -11,6 +11,9 @@
 // CTA writes each stage's mel values as contiguous row segments.
 #include "cac_common.cuh"
 #include "fft4096.cuh"
+#if CAC_FFT_PACKED
+#include "fft4096p.cuh"
+#endif
 
 namespace cac {
 
@@ -184,7 +187,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
         float vmax = 0.f;
 #pragma unroll 1
         for (int fi = warp; fi < nfs; fi += kWarpsPerCta) {
+#if CAC_FFT_PACKED
+            fft_frame_p<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt);
+#else
             fft_frame<POWER, K2N>(se, so, fi * a.hop, ex, pbuf, lane, lt);
+#endif
 #pragma unroll 1
             for (int i = 64 * K2N + lane; i < a.pbuf_len; i += 32) pbuf[i] = 0.f;  // zero-weight taps past the computed bins read zeros
             __syncwarp();
@@ -198,8 +205,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                 const int gm4 = slot.w;
                 // four independent partial sums (one per tap residue mod 4): fixed order, so deterministic,
                 // and the FMA chains of one group overlap instead of serialising on one accumulator
-                float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
                 const float4* const pend = pp + gm4;
+#if CAC_FFT_PACKED
+                float2 acc01 = make_float2(0.f, 0.f), acc23 = make_float2(0.f, 0.f);   // the same four partial sums, packed
+#pragma unroll 2
+                for (; pp != pend; ++pp, wg += 32) {
+                    const float4 w = *wg;
+                    const float4 p = *pp;
+                    acc01 = __ffma2_rn(make_float2(w.x, w.y), make_float2(p.x, p.y), acc01);
+                    acc23 = __ffma2_rn(make_float2(w.z, w.w), make_float2(p.z, p.w), acc23);
+                }
+                const float acc = ((acc01.x + acc01.y) + (acc23.x + acc23.y)) * sc;
+#else
+                float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
 #pragma unroll 2
                 for (; pp != pend; ++pp, wg += 32) {        // the padding taps add +0
                     const float4 w = *wg;
@@ -210,6 +228,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) stft_mel_kernel(const Fe
                     acc3 = fmaf(w.w, p.w, acc3);
                 }
                 const float acc = ((acc0 + acc1) + (acc2 + acc3)) * sc;
+#endif
                 if (slot.y >= 0) {
                     otile[slot.y + fi] = acc;
                     vmax = fmaxf(vmax, acc);

@@ -20,38 +20,37 @@ __device__ __forceinline__ unsigned valid_bits(int w, long long cols) {   // pix
 // ---- cv2.erode / cv2.dilate with a 1 x k rectangle: out(x) = OR | AND over d in [0, k) of in(x - k/2 + d) ----
 // pixels outside the image are ignored (cv2's morphology border).  Erosion runs as the complement of the
 // dilation of the complement (outside = 0 in the complemented domain is exactly "ignored").
+// One thread per output word, (row, word) flattened so that every CTA is full whatever the row length; the two or
+// three input words a thread needs come straight from L1 / L2 (the whole mask plane is 2.6 MB).
 template <bool IS_MAX>
-__global__ void __launch_bounds__(128) morph_h_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
-    extern __shared__ unsigned seg[];                 // words w0 - halo .. w0 + 127 + halo of this row
+__device__ __forceinline__ unsigned morph_word(const unsigned* row, int w, int wpr, long long cols) {
+    if (w < 0 || w >= wpr) return 0u;
+    const unsigned v = __ldg(row + w);
+    return IS_MAX ? v : (~v & valid_bits(w, cols));
+}
+template <bool IS_MAX>
+__global__ void __launch_bounds__(256) morph_h_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     const SnItem im = wv.items[blockIdx.z];
     const int wpr = im.wpr;
     const long long cols = im.cols;
-    const int halo = (k + 31) / 32 + 1;
-    const int w0 = blockIdx.x * 128;
-    if (w0 >= wpr) return;                            // shorter recording of the wave (uniform for the CTA)
-    const int r = blockIdx.y;
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long)wv.rows * wpr) return;
+    const int r = (int)(idx / wpr), w = (int)(idx - (long long)r * wpr);
     const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
     unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
     const unsigned* row = in + (size_t)r * wpr;
-    for (int i = threadIdx.x; i < 128 + 2 * halo; i += 128) {
-        const int w = w0 - halo + i;
-        unsigned v = 0u;
-        if (w >= 0 && w < wpr) {
-            v = row[w];
-            if (!IS_MAX) v = ~v & valid_bits(w, cols);
-        }
-        seg[i] = v;
-    }
-    __syncthreads();
-    const int w = w0 + threadIdx.x;
-    if (w >= wpr) return;
-    const int anchor = k / 2;
+    // window of 32 pixels starting at pixel 32 w - anchor + d, as a funnel shift over two neighbouring words
+    int bit = 32 * w - k / 2;                              // may be negative: arithmetic shift = floor division
+    int i = bit >> 5;
+    unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
     unsigned acc = 0u;
-    // window of 32 pixels starting at pixel 32 w - anchor + d, as a funnel shift over two staged words
-    int bit = 32 * (threadIdx.x + halo) - anchor;     // position inside seg, in pixels
     for (int d = 0; d < k; ++d, ++bit) {
-        const int i = bit >> 5;
-        acc |= __funnelshift_r(seg[i], seg[i + 1], bit & 31);
+        if ((bit >> 5) != i) {
+            i = bit >> 5;
+            lo = hi;
+            hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+        }
+        acc |= __funnelshift_r(lo, hi, bit & 31);
     }
     if (!IS_MAX) acc = ~acc;
     out[(size_t)r * wpr + w] = acc & valid_bits(w, cols);
@@ -59,21 +58,21 @@ __global__ void __launch_bounds__(128) morph_h_bits_kernel(const SnWave wv, int 
 
 // ---- k x 1 rectangle: OR | AND over the rows r - k/2 .. r - k/2 + k - 1 that exist --------------------
 template <bool IS_MAX>
-__global__ void __launch_bounds__(128) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
+__global__ void __launch_bounds__(256) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     const int wpr = wv.items[blockIdx.z].wpr;
     const int rows = wv.rows;
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long)rows * wpr) return;
+    const int r = (int)(idx / wpr), w = (int)(idx - (long long)r * wpr);
     const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
     unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
-    const int w = blockIdx.x * 128 + threadIdx.x;
-    const int r = blockIdx.y;
-    if (w >= wpr) return;
     const int r0 = max(r - k / 2, 0), r1 = min(r - k / 2 + k - 1, rows - 1);
     unsigned acc = IS_MAX ? 0u : 0xffffffffu;        // AND of real rows keeps the (zero) padding bits zero
     for (int rr = r0; rr <= r1; ++rr) {
-        const unsigned v = in[(size_t)rr * wpr + w];
+        const unsigned v = __ldg(in + (size_t)rr * wpr + w);
         acc = IS_MAX ? (acc | v) : (acc & v);
     }
-    out[(size_t)r * wpr + w] = acc;
+    out[idx] = acc;
 }
 
 __global__ void __launch_bounds__(256) unpack_bits_kernel(const SnWave wv, int plane, unsigned char* __restrict__ out_all,
@@ -255,14 +254,14 @@ __global__ void __launch_bounds__(256) stats_init_kernel(const SnWave wv) {
 // out = erode (is_max = false) / dilate (true) of plane `src` with a kh x kw rectangle; `tmp` is scratch
 cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp_plane, int dst_plane, int max_wpr, int kh,
                                          int kw, bool is_max, cudaStream_t st) {
-    dim3 grid((unsigned)((max_wpr + 127) / 128), (unsigned)w.rows, (unsigned)w.n_items);
-    const size_t smem = (128 + 2 * ((kw + 31) / 32 + 1)) * sizeof(unsigned);
+    const long long words = (long long)w.rows * max_wpr;
+    dim3 grid((unsigned)((words + 255) / 256), 1, (unsigned)w.n_items);
     if (is_max) {
-        morph_h_bits_kernel<true><<<grid, 128, smem, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<true><<<grid, 128, 0, st>>>(w, tmp_plane, dst_plane, kh);
+        morph_h_bits_kernel<true><<<grid, 256, 0, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<true><<<grid, 256, 0, st>>>(w, tmp_plane, dst_plane, kh);
     } else {
-        morph_h_bits_kernel<false><<<grid, 128, smem, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<false><<<grid, 128, 0, st>>>(w, tmp_plane, dst_plane, kh);
+        morph_h_bits_kernel<false><<<grid, 256, 0, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<false><<<grid, 256, 0, st>>>(w, tmp_plane, dst_plane, kh);
     }
     return cudaGetLastError();
 }

@@ -42,6 +42,7 @@ lib.cac_plan_destroy.argtypes = [_vp]
 lib.cac_plan_frames.argtypes = [_vp]
 lib.cac_plan_set_profiling.argtypes = [_vp, ctypes.c_int]
 lib.cac_plan_last_kernel_ms.argtypes = [_vp, ctypes.POINTER(ctypes.c_float)]
+lib.cac_measure_fp32_tflops.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
 lib.cac_plan_set_magtransform.argtypes = [_vp, ctypes.c_int, ctypes.c_float]
 lib.cac_features_work_bytes.argtypes = [_vp, _i64]
 lib.cac_features_work_bytes.restype = ctypes.c_size_t
@@ -105,7 +106,7 @@ lib.cac_resample_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
 EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resample_out_len", "cac_resample_run", "cac_spect_tail_run", "cac_sn_plan_create", "cac_sn_plan_destroy", "cac_sn_frame_count", "cac_sn_work_bytes", "cac_sn_run", "cac_sn_spectrum_run", "cac_signal_components_work_bytes", "cac_signal_components_run", "cac_get_end_work_bytes", "cac_get_end_run", "cac_host_register", "cac_host_unregister", "cac_magtransform_run", "cac_spec_plan_create", "cac_spec_plan_destroy", "cac_spec_frame_count", "cac_spec_rows", "cac_spec_run",
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
-           "cac_plan_frames", "cac_plan_set_magtransform", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
+           "cac_plan_frames", "cac_measure_fp32_tflops", "cac_plan_set_magtransform", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
            "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
 
 
@@ -120,6 +121,14 @@ def check(rc):
 
 def version():
     return lib.cac_version().decode()
+
+
+def measure_fp32_tflops(device=0):
+    """FP32 FFMA throughput of the device measured now (cac_measure_fp32_tflops): TFLOP/s."""
+    _torch()
+    v = ctypes.c_float()
+    check(lib.cac_measure_fp32_tflops(int(device), ctypes.byref(v)))
+    return float(v.value)
 
 
 def _torch():
@@ -655,14 +664,15 @@ class SignalNoisePlan:
         dev = torch.device("cuda", self.device)
         assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous() and pcm.dim() == 1
         cols = self.frame_count(pcm.numel())
-        spec = torch.empty((2049, cols), dtype=torch.float32, device=dev)
+        pitch = (cols + 31) // 32 * 32                            # rows padded to 32 floats (aligned 48-byte runs)
+        spec = torch.empty((2049, pitch), dtype=torch.float32, device=dev)
         colmed = torch.empty((cols,), dtype=torch.float32, device=dev)
         amax = torch.zeros((1,), dtype=torch.float32, device=dev)
         work = _work_buffer(self, 4096, dev)
         with torch.cuda.device(dev):
             check(lib.cac_sn_spectrum_run(self._h, pcm.data_ptr(), pcm.numel(), spec.data_ptr(), colmed.data_ptr(),
                                           amax.data_ptr(), work.data_ptr(), work.numel(), _stream_ptr(torch)))
-        return spec, colmed, amax
+        return spec[:, :cols], colmed, amax
 
 
 class _ComponentsScratch:

@@ -271,7 +271,7 @@ def signal_noise_spectrogram(frames, sr, hop_length=281):
     whole recording divided by its maximum, as a CUDA float32 tensor [2049, n_frames]."""
     plan = _signal_noise_plan(int(sr), int(hop_length))
     spec, _, a_max = plan.spectrum(to_device(frames, plan.device))
-    return spec.div_(a_max)                                       # IEEE float32 division, as numpy's
+    return (spec / a_max).contiguous()                            # IEEE float32 division, as numpy's
 
 
 SIGNAL_WIDTH = 0.25   # src/identify_tracks.py:21

@@ -34,8 +34,10 @@ class Signal:
         self.track_id = None
 
     def _refresh_mel(self):
-        self.mel_freq_start = mel_freq(self.freq_start)
-        self.mel_freq_end = mel_freq(self.freq_end)
+        # the same float64 values as the reference's numpy scalars, held as Python floats: the merge heuristics compare
+        # them O(n^2) times per sweep and numpy scalar arithmetic is several times slower than float arithmetic
+        self.mel_freq_start = float(mel_freq(self.freq_start))
+        self.mel_freq_end = float(mel_freq(self.freq_end))
 
     # -- geometry ------------------------------------------------------------------------------------------
     @property
@@ -101,23 +103,25 @@ class Signal:
 
 
 def _should_merge(s, u):
-    """The three merge rules of one (s, u) pair (src/identify_tracks.py:745-785); None = the pair is skipped."""
-    same_side = (u.mel_freq_end < 1500 and s.mel_freq_end < 1500) or (u.mel_freq_end > 1500 and s.mel_freq_end > 1500)
-    if not same_side:
+    """The three merge rules of one (s, u) pair (src/identify_tracks.py:745-785).  segment_overlap is written out
+    (same operations in the same order) because this runs O(n^2) times per sweep."""
+    sme, ume = s.mel_freq_end, u.mel_freq_end
+    if not ((ume < 1500 and sme < 1500) or (ume > 1500 and sme > 1500)):
         return False
-    t_overlap = s.time_overlap(u)
-    need = 0.5 if (s.mel_freq_start > 1000 and u.mel_freq_start > 1000) else 0.75
-    gap = s.start - u.end if s.start > u.end else u.start - s.end
-    m_overlap = s.mel_freq_overlap(u)
-    if t_overlap > u.length * 0.75 and m_overlap > -20:
+    ss, se, us, ue = s.start, s.end, u.start, u.end
+    sms, ums = s.mel_freq_start, u.mel_freq_start
+    t_overlap = (se - ss) + (ue - us) - (max(se, ue) - min(ss, us))
+    need = 0.5 if (sms > 1000 and ums > 1000) else 0.75
+    m_overlap = (sme - sms) + (ume - ums) - (max(sme, ume) - min(sms, ums))
+    u_range = ume - ums
+    if t_overlap > (ue - us) * 0.75 and m_overlap > -20:
         return True
-    if t_overlap > 0 and m_overlap > u.mel_freq_range * need:
+    if t_overlap > 0 and m_overlap > u_range * need:
         return True
-    if m_overlap > u.mel_freq_range * need and gap <= 2:
-        if u.mel_freq_end > s.mel_freq_range:
-            similar = s.mel_freq_range / u.mel_freq_range
-        else:
-            similar = u.mel_freq_range / s.mel_freq_range
+    gap = ss - ue if ss > ue else us - se
+    if m_overlap > u_range * need and gap <= 2:
+        s_range = sme - sms
+        similar = s_range / u_range if ume > s_range else u_range / s_range
         return similar >= 0.75
     return False
 
@@ -126,19 +130,18 @@ def merge_signals(signals):
     """One merging sweep (src/identify_tracks.py:725-792): signals ordered by start (ties: highest mel_freq_end first);
     each surviving signal absorbs the FIRST other survivor it may merge with.  Returns (signals, anything merged)."""
     ordered = sorted(sorted(signals, key=lambda s: s.mel_freq_end, reverse=True), key=lambda s: s.start)
-    dead = []
-    gone = lambda x: any(x is d for d in dead)
+    dead = set()                                   # ids: identity, like the reference's `in to_delete`
     for s in ordered:
-        if gone(s):
+        if id(s) in dead:
             continue
         for u in ordered:
-            if u is s or gone(u):
+            if u is s or id(u) in dead:
                 continue
             if _should_merge(s, u):
                 s.merge(u)
-                dead.append(u)
+                dead.add(id(u))
                 break
-    survivors = [s for s in ordered if not gone(s)]
+    survivors = [s for s in ordered if id(s) not in dead]
     return survivors, bool(dead)
 
 
@@ -150,22 +153,21 @@ def get_tracks_from_signals(signals, end):
     merged = True
     while merged:
         signals, merged = merge_signals(signals)
-    dead = []
-    gone = lambda x: any(x is d for d in dead)
+    dead = set()
     min_length = 0.35
     for s in signals:
-        if gone(s):
+        if id(s) in dead:
             continue
         if s.length < min_length:
-            dead.append(s)
+            dead.add(id(s))
             continue
         s.enlarge(1.4, min_track_length=0.7)
         s.end = min(end, s.end)
         for other in signals:
-            if other is s or gone(other):
+            if other is s or id(other) in dead:
                 continue
             min_length = min(s.length, other.length)
             if s.time_overlap(other) > 0.7 * min_length:
                 s.merge(other)
-                dead.append(other)
-    return [s for s in signals if not gone(s) and not s.mel_freq_range < 50]
+                dead.add(id(other))
+    return [s for s in signals if id(s) not in dead and not s.mel_freq_range < 50]

@@ -35,7 +35,7 @@ S1 = dict(hop_length=281, mel_break=1750, n_mels=160, fmin=50, fmax=11000, power
 SEG_LEN, STRIDE = 3.0, 1.5
 ALGO_BYTES_PER_REC = 11_520_000 + 39 * 160 * 513 * 4          # unique PCM in + dB out
 FLOP_PER_REC = 2.65e9
-FP32_PEAK_TFLOPS = 73.8     # measured on this pool: 36.9 T FFMA lane-ops/s (tools/micro/fp32x2_bench.cu, profiles/r1h_summary.md)
+FP32_PEAK_FALLBACK_TFLOPS = 73.8    # only if the in-run measurement (engine.measure_fp32_tflops) fails
 
 
 def _gen(seed):
@@ -135,7 +135,7 @@ def run_reference(args, rank, world):
         return
     cores = os.cpu_count() or 1
     per_step = max(4 * cores, 8)          # ~15-20 s of CPU work per step with one thread per core
-    for _ in range(args.warmup if args.warmup < 1 else 1):
+    for _ in range(min(args.warmup, 1)):      # the CPU arm has no clocks or caches to warm beyond the first import
         cpu_oracle_rate(min(cores, per_step), cores)
     rates, walls = [], []
     for _ in range(args.steps):
@@ -150,7 +150,7 @@ def run_reference(args, rank, world):
         "unit": "recording-hours/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1000.0 * sum(walls) / len(walls), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(sample_note=sample),
+        "config": workload_config(), "sample": sample,
         "cpu_baseline": {"value": value, "unit": "recording-hours/s", "cores": cores, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": "recording-hours/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -159,7 +159,7 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(sample_note=None):
+def workload_config():
     c = {"workload": "configs[1]: %d x 60 s 48 kHz recordings per GPU, load_samples S1 (n_fft 4096, hop 281, "
                      "160 mels 50-11000 Hz break 1750, power 2, power_to_db, normalize), 39 segments each" % N_REC,
          "recordings_per_gpu": N_REC, "segments_per_recording": 39, "unique_recordings_per_gpu": POOL,
@@ -167,8 +167,6 @@ def workload_config(sample_note=None):
     if WAVES > 1:
         c["waves_per_step"] = WAVES
         c["workload"] += "; %d waves per step (configs[4]-style sharded run, per-recording results gathered once per step)" % WAVES
-    if sample_note:
-        c["sample"] = sample_note
     return c
 
 
@@ -180,6 +178,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
+    ap.add_argument("--no-paths", action="store_true", help="skip the `paths` object (other configs, pipeline)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -251,7 +250,8 @@ def main():
         return None
 
     # ---- device-resident timing ---------------------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
+    warmup_done = max(args.warmup, 3)                      # the timing rules ask for at least three
+    for _ in range(warmup_done):
         step()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -278,44 +278,112 @@ def main():
     seg_chunk = descriptors(chunk)
     h2d_bytes = int(n_chunks * (chunk * n_samp * 4 + seg_chunk.nbytes))
     d2h_bytes = int(n_chunks * chunk * nseg1 * 160 * plan.n_frames * 4)
+    e2e_steps = args.steps
+    e2e_s = e2e16_s = e2e_dev_s = float("nan")
+    ceiling = None
     if not args.no_e2e:
         out_host_t = torch.empty((chunk * nseg1, 160, plan.n_frames), dtype=torch.float32).pin_memory()
         out_host = out_host_t.numpy()
         # physically distinct host copies of every recording of a call (the pool repeated), page-locked
         host_in_t = pool_pinned.repeat((chunk + POOL - 1) // POOL, 1)[:chunk].contiguous().pin_memory()
         pool_np = host_in_t.numpy().reshape(-1)
-
         # the same recordings as 16-bit PCM (what a decoder delivers): half the upload
         host_in16_t = torch.from_numpy(np.round(pool_np * 32767.0).astype(np.int16)).pin_memory()
         pool_np16 = host_in16_t.numpy()
 
-    def e2e_step(pcm16=False):
-        for _ in range(n_chunks):
-            plan.run_host(pool_np16 if pcm16 else pool_np, seg_chunk, out_host)
+        def e2e_step(pcm16=False):
+            for _ in range(n_chunks):
+                plan.run_host(pool_np16 if pcm16 else pool_np, seg_chunk, out_host)
 
-    e2e_s = e2e16_s = float("nan")
-    if not args.no_e2e:
-        e2e_step()
+        def timed_wall(fn):
+            fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                fn()
+            barrier()
+            return (time.perf_counter() - t0) / e2e_steps
+
+        e2e_s = timed_wall(e2e_step)
+        e2e16_s = timed_wall(lambda: e2e_step(pcm16=True))
+
+        # the deployment north_star describes for a classifier on the GPU: PCM up, segments stay on the device
+        # (load_samples_device), only the per-segment maxima come back.  Uploads of call k + 1 overlap the kernels of call k.
+        up_stream = torch.cuda.Stream(device=dev)
+        dev_in = [torch.empty(chunk * n_samp, dtype=torch.float32, device=dev) for _ in range(2)]
+        segc_dev = torch.from_numpy(seg_chunk.view(np.uint8).reshape(-1)).to(dev)
+        out_c = out[: chunk * nseg1]
+        maxima_host = torch.empty((n_chunks, chunk * nseg1), dtype=torch.float32).pin_memory()
+        flat_in = host_in_t.reshape(-1)
+
+        def e2e_device_step():
+            cur = torch.cuda.current_stream(dev)
+            ups, done = [], []
+            for c in range(n_chunks):
+                with torch.cuda.stream(up_stream):
+                    if c >= 2:
+                        up_stream.wait_event(done[c - 2])           # the buffer's previous consumer has finished
+                    dev_in[c & 1].copy_(flat_in, non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(up_stream)
+                    ups.append(ev)
+                cur.wait_event(ups[c])
+                plan.run(dev_in[c & 1], segc_dev, out_c)
+                maxima_host[c].copy_(plan.last_segment_max(chunk * nseg1), non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                done.append(ev)
+            cur.synchronize()
+
+        e2e_dev_s = timed_wall(e2e_device_step)
+        assert bool((maxima_host > 0).all())
+
+        # what this box lets `world` ranks copy at the same time: H2D and D2H of 1 GiB each, concurrently, from
+        # page-locked memory allocated after the NUMA binding - the ceiling e2e can be read against
+        probe_n = 1 << 28
+        ph = torch.empty(probe_n, dtype=torch.float32).pin_memory()
+        pd = torch.empty(probe_n, dtype=torch.float32, device=dev)
+        qh = torch.empty(probe_n, dtype=torch.float32).pin_memory()
+        qd = torch.empty(probe_n, dtype=torch.float32, device=dev)
+        s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+        def both():
+            with torch.cuda.stream(s1):
+                pd.copy_(ph, non_blocking=True)
+            with torch.cuda.stream(s2):
+                qh.copy_(qd, non_blocking=True)
+            s1.synchronize()
+            s2.synchronize()
+
+        def up_only():
+            with torch.cuda.stream(s1):
+                pd.copy_(ph, non_blocking=True)
+            s1.synchronize()
+
+        reps = 4
+        both()
         barrier()
         t0 = time.perf_counter()
-        e2e_steps = max(1, min(args.steps, 3))
-        for _ in range(e2e_steps):
-            e2e_step()
+        for _ in range(reps):
+            both()
         barrier()
-        e2e_s = (time.perf_counter() - t0) / e2e_steps
-        e2e_step(pcm16=True)
+        t_both = (time.perf_counter() - t0) / reps
+        up_only()
         barrier()
         t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step(pcm16=True)
+        for _ in range(reps):
+            up_only()
         barrier()
-        e2e16_s = (time.perf_counter() - t0) / e2e_steps
+        t_up = (time.perf_counter() - t0) / reps
+        ceiling = [probe_n * 4 / t_both / 1e9, probe_n * 4 / t_up / 1e9]
+        ph = pd = qh = qd = dev_in = out_c = None
 
     # ---- reduce over ranks (max time) -------------------------------------------------------------------
-    t = torch.tensor([total_ms, e2e_s, float(np.median(kernel_ms)), e2e16_s], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_s, float(np.median(kernel_ms)), e2e16_s, e2e_dev_s] + [-c for c in (ceiling or [0.0, 0.0])],
+                     dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_s, k_ms, e2e16_s = (float(v) for v in t.tolist())
+    total_ms, e2e_s, k_ms, e2e16_s, e2e_dev_s, neg_both, neg_up = (float(v) for v in t.tolist())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -327,37 +395,54 @@ def main():
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    try:
+        fp32_peak, fp32_src = engine.measure_fp32_tflops(local_rank), "measured in this run (cac_measure_fp32_tflops, FFMA)"
+    except Exception as exc:          # keep the line; say what happened
+        fp32_peak, fp32_src = FP32_PEAK_FALLBACK_TFLOPS, "fallback constant (%s)" % exc
     rec_hours = world * WAVES * N_REC * REC_SECONDS / 3600.0
+    job_hours = world * N_REC * REC_SECONDS / 3600.0
     ms_per_step = total_ms / args.steps
     achieved = ALGO_BYTES_PER_REC * N_REC / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("stft_mel_bytes_per_launch")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get("stft_mel_bytes_per_launch")
+        traffic_src = "NOT measured in this run: dram__bytes_read.sum + dram__bytes_write.sum from %s (profiles/traffic.json)" % tj.get("source", "?")
     except Exception:
         pass
     line = {
         "metric": "recording-hours/sec (STFT->mel->dB)", "value": rec_hours / (ms_per_step * 1e-3),
-        "unit": "recording-hours/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(),
-        "e2e": {"value": (world * N_REC * REC_SECONDS / 3600.0) / e2e_s, "unit": "recording-hours/s",
-                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_s * 1e3,
+        "unit": "recording-hours/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "warmup_done": warmup_done, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(),
+        "host_affinity": ("%d CPUs next to the GPU (NVML)" % len(numa_cpus)) if numa_cpus else "unchanged",
+        "e2e": {"value": job_hours / e2e_s, "unit": "recording-hours/s",
+                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+                "gbs_per_rank": (h2d_bytes + d2h_bytes) / e2e_s / 1e9 if e2e_s == e2e_s else None,
+                "copy_ceiling_gbs": None if ceiling is None else {
+                    "h2d_while_d2h_per_rank": -neg_both, "h2d_alone_per_rank": -neg_up,
+                    "note": "slowest rank; %d ranks copying 1 GiB each way at the same time from page-locked memory" % world},
                 "api": "FeaturePlan.run_host -> cac_features_host (3-stream upload/compute/download pipeline, pinned host buffers), %d recordings per call" % chunk},
-        "e2e_pcm16": {"value": (world * N_REC * REC_SECONDS / 3600.0) / e2e16_s, "unit": "recording-hours/s",
+        "e2e_pcm16": {"value": job_hours / e2e16_s, "unit": "recording-hours/s",
                       "h2d_bytes_per_step": int(n_chunks * (chunk * n_samp * 2 + seg_chunk.nbytes)),
                       "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e16_s * 1e3,
                       "note": "same call with the recordings as 16-bit PCM (cac_features_host_pcm16): not the headline, the reference hands over float32"},
+        "e2e_device_consumer": {"value": job_hours / e2e_dev_s, "unit": "recording-hours/s", "h2d_bytes_per_step": h2d_bytes,
+                                "d2h_bytes_per_step": int(n_chunks * chunk * nseg1 * 4), "ms_per_step": e2e_dev_s * 1e3,
+                                "note": "NOT the headline: PCM uploaded from pinned memory every step, the segments stay on the GPU "
+                                        "for a classifier there (load_samples_device), only the per-segment maxima come back"},
         "gpu_launches": 3 * WAVES * args.steps,
         "kernels_per_step": ["seg_minmax_kernel", "stft_mel_kernel<2>", "power_to_db_kernel"],
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "stft_mel_kernel<2>",
+                     "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "kernel": "stft_mel_kernel<2>",
                      "kernel_ms": k_ms, "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback",
                      "fp32_tflops": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12,
-                     "fp32_frac_of_measured_peak": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12 / FP32_PEAK_TFLOPS,
+                     "fp32_peak_tflops": fp32_peak, "fp32_peak_source": fp32_src,
+                     "fp32_frac_of_measured_peak": FLOP_PER_REC * N_REC / (k_ms * 1e-3) / 1e12 / fp32_peak,
                      "note": "FP32-pipe bound (75-110 flop/B, SURVEY.md 8d); HBM fraction reported as the metric asks"},
         "clocks": clocks, "checksum_first_recording": checksum,
     }
-    line["config"]["host_affinity"] = ("%d CPUs next to the GPU (NVML)" % len(numa_cpus)) if numa_cpus else "unchanged"
     if world == 1 and not args.no_cpu_baseline:
         os.sched_setaffinity(0, all_cpus)                  # the CPU baseline may use every host core again
         cores = os.cpu_count() or 1
@@ -367,6 +452,21 @@ def main():
         line["cpu_baseline"] = {"value": v, "unit": "recording-hours/s", "cores": cores, "kind": "port",
                                 "sample": "%d one-minute recordings, %d processes x 1 thread, %.1f s wall; single process with default threading: %.5f rec-h/s"
                                           % (n, cores, wall, v1)}
+    if world == 1 and not args.no_paths:
+        # the other BASELINE.json configs and the per-recording pipeline, each a few seconds (tools/bench_paths.py)
+        out = pcm = segs_dev = wave_results = pool_dev = None      # (cells shared with the step closures)
+        if not args.no_e2e:
+            out_host_t = out_host = host_in_t = pool_np = host_in16_t = pool_np16 = maxima_host = flat_in = None
+        torch.cuda.empty_cache()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_paths
+        line["paths"] = {}
+        for name in ("single", "pipeline", "morepork", "ci"):
+            try:
+                line["paths"][name] = bench_paths.PATHS[name](cpu=not args.no_cpu_baseline)
+            except Exception as exc:     # a failing side path must not take the headline line with it
+                line["paths"][name] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+            torch.cuda.empty_cache()
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -90,6 +90,9 @@ int cac_plan_last_kernel_ms(cac_plan* plan, float* ms);
  * powf per value in the kernel's flush instead of another read and write of the whole output (cac_magtransform_run).
  * Only for plans with db_scale = 0 that the fused kernel serves (n_fft 4096, bands below bin 1024). */
 int cac_plan_set_magtransform(cac_plan* plan, int enable, float a);
+/* Measurement hook (no reference counterpart): FP32 FFMA throughput the device sustains (2 flop per lane-operation,
+ * TFLOP/s, best of three ~5 ms launches) - the denominator of bench.py's FP32 fraction, measured in the same run. */
+int cac_measure_fp32_tflops(int device, float* tflops);
 /* Bytes of device scratch cac_features_run needs for n_segments (the unfused path adds the normalised segment rows). */
 size_t cac_features_work_bytes(const cac_plan* plan, int64_t n_segments);
 
@@ -243,8 +246,9 @@ size_t cac_sn_work_bytes(const cac_sn_plan* plan, int64_t n_items, int64_t max_i
 int cac_sn_run(cac_sn_plan* plan, const float* d_pcm, const int64_t* d_item_offset, const int64_t* d_item_samples,
                int64_t n_items, int64_t max_item_samples, int32_t max_components, int32_t* d_result, void* d_work,
                size_t work_bytes, void* stream);
-/* The first stage alone for one recording (:652-656): d_spec [2049][cols] = |stft| (not yet divided by its maximum),
- * d_colmed [cols] = np.median(|stft|, axis=0), *d_amax = np.amax(|stft|).  d_work: 512 bytes, 256-byte aligned. */
+/* The first stage alone for one recording (:652-656): d_spec [2049][pitch] = |stft| (not yet divided by its maximum;
+ * pitch = cols rounded up to a multiple of 32 floats, the kernel writes 16-byte aligned runs; columns >= cols are
+ * not written), d_colmed [cols] = np.median(|stft|, axis=0), *d_amax = np.amax(|stft|).  d_work: 512 bytes, 256-byte aligned. */
 int cac_sn_spectrum_run(cac_sn_plan* plan, const float* d_pcm, int64_t n_samples, float* d_spec, float* d_colmed,
                         float* d_amax, void* d_work, size_t work_bytes, void* stream);
 
