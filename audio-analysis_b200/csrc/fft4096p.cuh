@@ -5,7 +5,7 @@
 // slots; the FP32 pipe time is unchanged
 // (a packed instruction occupies the pipe for two cycles), so this helps exactly where the kernel is bound by
 // issue slots rather than by the pipe (profiles/r2j_summary.md: issue active 69 %, FMA pipe 52 %).
-// Selected with -DCAC_FFT_PACKED=1 (stft_mel.cu, sn_stft.cu).
+// The default; -DCAC_FFT_PACKED=0 selects the scalar form (stft_mel.cu, sn_stft.cu).
 #pragma once
 #include "fft4096.cuh"
 #include "fft_pairs.cuh"

@@ -9,13 +9,26 @@
 // row is formed on the spot from fl(x / a_max) - bit-identical to the reference's arithmetic - and written bit-packed
 // (32 cells per ballot).  The scaled matrix, the transposed matrix and the separate mask pass of the first version
 // (5 reads + 2 writes of the 84 MB matrix per minute of audio) are gone.
+#include <cstdlib>
+
 #include "cac_common.cuh"
 #include "sn.cuh"
 #include "sn_select.cuh"
 
 namespace cac {
 
-// colthr[c] = fl(3 * fl(colmed[c] / a_max)): the column threshold, once per column instead of once per cell
+// The reference compares fl(x / a_max) with a threshold t.  fl(x / a) is monotone in x, so that comparison equals
+// x > x_t with x_t = the largest float whose quotient still rounds to <= t: one or two divisions per THRESHOLD (the
+// product t a is within an ulp or two of x_t; it is walked to the exact boundary) instead of one per CELL.
+__device__ __forceinline__ float unscaled_threshold(float t, float a) {
+    if (!(a > 0.f)) return INFINITY;                  // silent recording: 0 / 0 = NaN, nothing exceeds a threshold
+    unsigned y = __float_as_uint(__fmul_rn(t, a));
+    while (y > 0u && __fdiv_rn(__uint_as_float(y), a) > t) --y;
+    while (y < 0x7f7fffffu && __fdiv_rn(__uint_as_float(y + 1u), a) <= t) ++y;
+    return __uint_as_float(y);
+}
+
+// colthr[c] = x_t of t = fl(3 * fl(colmed[c] / a_max)): the column threshold in the unscaled domain, once per column
 __global__ void __launch_bounds__(256) sn_col_thresholds_kernel(const SnWave w) {
     const int item = blockIdx.y;
     const int cols = w.items[item].cols;
@@ -23,7 +36,7 @@ __global__ void __launch_bounds__(256) sn_col_thresholds_kernel(const SnWave w) 
     if (c >= cols) return;
     const float a = __uint_as_float(w.amax[item]);
     const size_t o = (size_t)item * w.col_stride + c;
-    w.colthr[o] = __fmul_rn(3.0f, __fdiv_rn(w.colmed[o], a));
+    w.colthr[o] = unscaled_threshold(__fmul_rn(3.0f, __fdiv_rn(w.colmed[o], a)), a);
 }
 
 struct RowSel {                       // shared scratch of one CTA's select
@@ -59,8 +72,8 @@ __device__ __forceinline__ float scaled_median(unsigned v1, unsigned cnt_le, uns
 }
 
 // NT threads hold PER keys each, element i of thread t = column t + NT i (a warp's 32 lanes = one mask word).
-template <int NT, int PER>
-__global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
+template <int NT, int PER, int MINB = 1>
+__global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_kernel(const SnWave w) {
     __shared__ __align__(16) RowSel s;
     const int item = blockIdx.y, row = blockIdx.x;
     const SnItem im = w.items[item];
@@ -97,7 +110,7 @@ __global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
             __syncthreads();
 #pragma unroll
             for (int i = 0; i < PER; ++i)
-                smem_inc_if(s.hist + ((key[i] >> shift) & dmask), tid + NT * i < cols && ((key[i] ^ prefix) & above) == 0u);
+                if (tid + NT * i < cols && ((key[i] ^ prefix) & above) == 0u) atomicAdd(s.hist + ((key[i] >> shift) & dmask), 1u);
             __syncthreads();
             sel_scan_cta<NT>(s.hist, k, s.tot, s.out);
             prefix |= s.out[0] << shift;
@@ -122,7 +135,7 @@ __global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
         __syncthreads();
     }
     const float a = __uint_as_float(w.amax[item]);
-    const float tr = __fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a));
+    const float tr = unscaled_threshold(__fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a)), a);
     const float* thr = w.colthr + (size_t)item * w.col_stride;
     unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
 #pragma unroll
@@ -130,8 +143,8 @@ __global__ void __launch_bounds__(NT) sn_rowmed_mask_kernel(const SnWave w) {
         const int c = tid + NT * i;
         bool on = false;
         if (c < cols) {
-            const float xn = __fdiv_rn(__uint_as_float(key[i]), a);
-            on = xn > __ldg(thr + c) && xn > tr;
+            const float x = __uint_as_float(key[i]);
+            on = x > __ldg(thr + c) && x > tr;           // == fl(x / a) > 3 column median && fl(x / a) > 3 row median
         }
         const unsigned word = __ballot_sync(0xffffffffu, on);
         if (lane == 0 && (c >> 5) < im.wpr) bits[c >> 5] = word;
@@ -169,7 +182,7 @@ __global__ void __launch_bounds__(256) sn_rowmed_mask_long_kernel(const SnWave w
             __syncthreads();
             for (int c = tid; c < cols; c += NT) {
                 const unsigned key = rowp[c];
-                smem_inc_if(s.hist + ((key >> shift) & dmask), ((key ^ prefix) & above) == 0u);
+                if (((key ^ prefix) & above) == 0u) atomicAdd(s.hist + ((key >> shift) & dmask), 1u);
             }
             __syncthreads();
             sel_scan_cta<NT>(s.hist, k, s.tot, s.out);
@@ -194,15 +207,15 @@ __global__ void __launch_bounds__(256) sn_rowmed_mask_long_kernel(const SnWave w
         __syncthreads();
     }
     const float a = __uint_as_float(w.amax[item]);
-    const float tr = __fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a));
+    const float tr = unscaled_threshold(__fmul_rn(3.0f, scaled_median(v1, s.cnt_le, s.min_gt, cols, a)), a);
     const float* thr = w.colthr + (size_t)item * w.col_stride;
     unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
     for (int c0 = 0; c0 < cols; c0 += NT) {                 // uniform trip count: every lane reaches the ballot
         const int c = c0 + tid;
         bool on = false;
         if (c < cols) {
-            const float xn = __fdiv_rn(__uint_as_float(rowp[c]), a);
-            on = xn > thr[c] && xn > tr;
+            const float x = __uint_as_float(rowp[c]);
+            on = x > thr[c] && x > tr;
         }
         const unsigned word = __ballot_sync(0xffffffffu, on);
         if (lane == 0 && (c >> 5) < im.wpr) bits[c >> 5] = word;
@@ -222,7 +235,15 @@ cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, cudaStream_t st
     if (max_cols <= 256 * 8) sn_rowmed_mask_kernel<256, 8><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 16) sn_rowmed_mask_kernel<256, 16><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 32) sn_rowmed_mask_kernel<256, 32><<<grid, 256, 0, st>>>(w);
-    else if (max_cols <= 256 * 44) sn_rowmed_mask_kernel<256, 44><<<grid, 256, 0, st>>>(w);   // one-minute recordings: 10,250
+    else if (max_cols <= 256 * 44) {                      // one-minute recordings: 10,250 columns
+        // 512 threads x 22 keys at two CTAs per SM: measured fastest of {256 x 44, 512 x 22, 1024 x 11} (0.38 / 0.28 /
+        // 0.30-0.34 ms per recording for the whole chain, profiles/r3_experiments.md); CAC_SN_ROWS_VARIANT picks another
+        static const int variant = getenv("CAC_SN_ROWS_VARIANT") ? atoi(getenv("CAC_SN_ROWS_VARIANT")) : 1;
+        if (variant == 0) sn_rowmed_mask_kernel<256, 44><<<grid, 256, 0, st>>>(w);
+        else if (variant == 2) sn_rowmed_mask_kernel<1024, 11, 1><<<grid, 1024, 0, st>>>(w);
+        else if (variant == 3) sn_rowmed_mask_kernel<1024, 11, 2><<<grid, 1024, 0, st>>>(w);
+        else sn_rowmed_mask_kernel<512, 22, 2><<<grid, 512, 0, st>>>(w);
+    }
     else {
         sn_rowmed_mask_kernel<512, 48><<<grid, 512, 0, st>>>(w);         // rows up to 24,576 columns
         if (max_cols > kSnMaxColsFast) sn_rowmed_mask_long_kernel<<<grid, 256, 0, st>>>(w);   // the longer ones

@@ -4,8 +4,8 @@
 // starts below the common prefix of the smallest and the largest key and takes wide digits (11 bits per pass for a
 // warp's private histogram, 12 for a CTA's): two or three passes instead of four 8-bit ones, and the first pass
 // spreads over hundreds of bins instead of the two or three exponent bytes (no same-address serialisation).
-// Histogram updates are single predicated `red.shared` instructions (an `if` around atomicAdd compiles to a
-// branch with a reconvergence barrier per element; ncu showed those branches, not the atomics, as the cost).
+// Histogram updates are unconditional atomics whose ADDRESS is selected (elements outside the current prefix go to a
+// throw-away word): no branch per element.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -14,9 +14,11 @@ namespace cac {
 constexpr int kSelWarpBits = 11, kSelWarpBins = 1 << kSelWarpBits;   // 8 KB per warp
 constexpr int kSelCtaBits = 12, kSelCtaBins = 1 << kSelCtaBits;      // 16 KB per CTA
 
-__device__ __forceinline__ void smem_inc_if(unsigned* addr, bool p) {
-    const unsigned a = (unsigned)__cvta_generic_to_shared(addr);
-    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %1, 0;\n\t@q red.shared.add.u32 [%0], 1;\n\t}" ::"r"(a), "r"((unsigned)p) : "memory");
+// hist[bin] += 1 when p, else a throw-away word: ONE unconditional shared-memory atomic.  (`if (p) atomicAdd` and a
+// predicated `red.shared` both compile to a branch with a reconvergence barrier around ATOMS - ncu showed
+// branch_resolving at 20-25 % of the select's stall samples; a select of the address costs nothing of the kind.)
+__device__ __forceinline__ void smem_inc_sel(unsigned* hist, unsigned bin, bool p, unsigned* trash) {
+    atomicAdd(p ? hist + bin : trash, 1u);
 }
 
 // One warp finds the bin of its 2048-bin histogram that holds rank k (0-based, k < total): returns the bin, k becomes

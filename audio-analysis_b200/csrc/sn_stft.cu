@@ -44,6 +44,7 @@ __device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], floa
     unsigned prefix = (mx >> top) << top;
     unsigned k = 1024u;
     uint4* h4 = reinterpret_cast<uint4*>(hist);
+    unsigned* trash = hist + kSelWarpBins + lane;         // the warp's buffer has 2,112 words: 32 spare ones per lane
     const unsigned ekey = __float_as_uint(nyq);
     int remaining = top;
 #pragma unroll 1
@@ -56,9 +57,9 @@ __device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], floa
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
             const unsigned key = __float_as_uint(v[i]);
-            smem_inc_if(hist + ((key >> shift) & dmask), ((key ^ prefix) >> remaining) == 0u);
+            smem_inc_sel(hist, (key >> shift) & dmask, ((key ^ prefix) >> remaining) == 0u, trash);
         }
-        smem_inc_if(hist + ((ekey >> shift) & dmask), lane == 0 && ((ekey ^ prefix) >> remaining) == 0u);
+        if (lane == 0) smem_inc_sel(hist, (ekey >> shift) & dmask, ((ekey ^ prefix) >> remaining) == 0u, trash);
         __syncwarp();
         const unsigned digit = sel_scan_warp(hist, lane, k);
         prefix |= digit << shift;
@@ -159,14 +160,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
                 float* orow = spec + (size_t)tid * im.pitch + (f0 + r0);
                 const size_t ostep = (size_t)(kWarpsPerCta * 32) * im.pitch;
                 if (nr == kWarpsPerCta) {      // f0 + r0 is a multiple of 4 and the pitch of 32: 16-byte aligned runs
-                    for (int bin = tid; bin < kSnRows; bin += kWarpsPerCta * 32, orow += ostep) {
-                        float4* o4 = reinterpret_cast<float4*>(orow);
-#pragma unroll
-                        for (int q = 0; q < kWarpsPerCta / 4; ++q) {
-                            const float* t = tile + (4 * q) * kExFloats + bin;
-                            o4[q] = make_float4(0.5f * t[0], 0.5f * t[kExFloats], 0.5f * t[2 * kExFloats], 0.5f * t[3 * kExFloats]);
-                        }
-                    }
+                    // three consecutive lanes write the three 16-byte quarters of one bin's 48-byte run: a warp's store
+                    // covers 10 contiguous runs (20 sectors) instead of 32 scattered 16-byte pieces (32 sectors)
+                    constexpr int kRowsPerIt = kWarpsPerCta * 32 / 3;
+                    const int sub = tid / 3, q = tid - 3 * sub;
+                    const float* t = tile + (4 * q) * kExFloats;
+                    float* o = spec + (size_t)sub * im.pitch + (f0 + r0) + 4 * q;
+                    for (int bin = sub; bin < kSnRows; bin += kRowsPerIt, o += (size_t)kRowsPerIt * im.pitch)
+                        *reinterpret_cast<float4*>(o) = make_float4(0.5f * t[bin], 0.5f * t[kExFloats + bin],
+                                                                    0.5f * t[2 * kExFloats + bin], 0.5f * t[3 * kExFloats + bin]);
                 } else {
                     for (int bin = tid; bin < kSnRows; bin += kWarpsPerCta * 32, orow += ostep)
                         for (int j = 0; j < nr; ++j) orow[j] = 0.5f * tile[j * kExFloats + bin];

@@ -39,18 +39,38 @@ __global__ void __launch_bounds__(256) morph_h_bits_kernel(const SnWave wv, int 
     const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
     unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
     const unsigned* row = in + (size_t)r * wpr;
-    // window of 32 pixels starting at pixel 32 w - anchor + d, as a funnel shift over two neighbouring words
+    // out = OR over d in [0, k) of the 32-pixel window starting at pixel 32 w - anchor + d
     int bit = 32 * w - k / 2;                              // may be negative: arithmetic shift = floor division
     int i = bit >> 5;
-    unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
     unsigned acc = 0u;
-    for (int d = 0; d < k; ++d, ++bit) {
-        if ((bit >> 5) != i) {
-            i = bit >> 5;
-            lo = hi;
-            hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+    if (k <= 64) {
+        // the windows all lie inside words i .. i + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
+        // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k
+        unsigned A[5];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) A[j] = morph_word<IS_MAX>(row, i + j, wpr, cols);
+        A[4] = 0u;
+        int m = 1;
+        for (; 2 * m <= k; m <<= 1) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
         }
-        acc |= __funnelshift_r(lo, hi, bit & 31);
+        const int rest = k - m;                            // < m <= 32
+        if (rest) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
+        }
+        acc = __funnelshift_rc(A[0], A[1], bit & 31);
+    } else {
+        unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+        for (int d = 0; d < k; ++d, ++bit) {
+            if ((bit >> 5) != i) {
+                i = bit >> 5;
+                lo = hi;
+                hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+            }
+            acc |= __funnelshift_r(lo, hi, bit & 31);
+        }
     }
     if (!IS_MAX) acc = ~acc;
     out[(size_t)r * wpr + w] = acc & valid_bits(w, cols);

@@ -190,7 +190,7 @@ class FeaturePlan:
         if isinstance(segments, np.ndarray):
             assert segments.dtype == SEGMENT_DTYPE
             n = segments.shape[0]
-            segments = torch.from_numpy(segments.view(np.uint8).reshape(-1)).to(dev)
+            segments = self._stage_segments(torch, dev, segments)
         else:
             n = segments.numel() * segments.element_size() // 16
         assert pcm.is_cuda and pcm.dtype == torch.float32 and pcm.is_contiguous()
@@ -202,6 +202,21 @@ class FeaturePlan:
         with torch.cuda.device(dev):
             check(lib.cac_features_run(self._h, pcm.data_ptr(), segments.data_ptr(), n, out.data_ptr(),
                                        self._work.data_ptr(), _stream_ptr(torch)))
+        return out
+
+    def _stage_segments(self, torch, dev, segments):
+        """Descriptor table -> device through a page-locked staging buffer and an ASYNCHRONOUS copy: a pageable upload
+        would make the host wait for everything already queued on the stream (classify_prep_batch queues the next chunk's
+        kernels before it gets here)."""
+        raw = np.ascontiguousarray(segments).view(np.uint8).reshape(-1)
+        if getattr(self, "_seg_done", None) is not None:
+            self._seg_done.synchronize()                   # the previous copy out of the staging buffer has finished
+        if getattr(self, "_seg_pin", None) is None or self._seg_pin.numel() < raw.size:
+            self._seg_pin = torch.empty(max(raw.size, 1 << 16), dtype=torch.uint8).pin_memory()
+        self._seg_pin[:raw.size].numpy()[:] = raw
+        out = self._seg_pin[:raw.size].to(dev, non_blocking=True)
+        self._seg_done = torch.cuda.Event()
+        self._seg_done.record()
         return out
 
     def last_segment_max(self, n):

@@ -331,14 +331,17 @@ def signal_noise(frames, sr, hop_length=281, signal_cls=None):
 
 def classify_prep_batch(recordings, sr, segment_length=3, segment_stride=1.5, hop_length=281, mean_sub=False,
                         mel_break=1000, htk=True, n_mels=160, fmin=50, fmax=11000, channels=1, power=2, db_scale=False,
-                        normalize=True, n_fft=4096, pad_short_tracks=False, max_components=4096, want_samples=True):
+                        normalize=True, n_fft=4096, pad_short_tracks=False, max_components=1024, want_samples=True,
+                        chunk=64):
     """Everything classify does to a recording before its model runs (src/identify_tracks.py:416-440, 502-524) for a
-    batch of decoded recordings, with TWO synchronisations in total:
+    batch of decoded recordings.  The batch goes through in chunks of `chunk` recordings, and per chunk:
       1. get_end -> signal_noise(frames[: int(sr * length)]) chained on the device (the trimmed lengths are computed on
-         the GPU from get_end's chunk index and handed to cac_sn_run as its device item table), one copy brings back
-         the end chunks and the component tables of all recordings;
-      2. the host turns components into signals and tracks (get_tracks_from_signals, O(100) boxes per recording), and
-         ONE cac_features_run produces the classifier segments of every track of every recording on the device.
+         the GPU from get_end's chunk index and handed to cac_sn_run as its device item table); one asynchronous copy
+         brings the end chunks and the component tables of the chunk back into page-locked memory;
+      2. the host turns components into signals and tracks (get_tracks_from_signals, O(100) boxes per recording) and
+         ONE cac_features_run per chunk produces the classifier segments of every track on the device.
+    The GPU work of chunk i + 1 is queued before the host waits for chunk i, so the host's scalar merge logic overlaps
+    the kernels; a single recording costs two synchronisations.
     Returns one dict per recording: tracks, length, signals (copies taken before the merge, as classify keeps them for
     the chirp count), raw_length, and samples = one CUDA tensor [n_segments, n_mels, frames, channels] per track
     (what load_samples_device returns; None when want_samples is False).  Consumes np.random like load_samples."""
@@ -353,47 +356,70 @@ def classify_prep_batch(recordings, sr, segment_length=3, segment_stride=1.5, ho
     dev = flat.device
     chunk_length = sr // 281
     max_len = int(lens.max())
+    rstride = 4 + 6 * int(max_components)
     tables = torch.from_numpy(np.stack([offs, lens, np.array([int(sr * (int(m) / sr)) for m in lens], dtype=np.int64)])).to(dev)
-    first = ge.get_end_chunks(flat, tables[0], tables[1], chunk_length, max_item_samples=max_len)
-    # frames[: int(sr * length)] with length = chunk * chunk_length * 281 // sr whole seconds, or len / sr (:387-420)
-    first64 = first.to(torch.int64)
-    secs = torch.div(first64 * (chunk_length * 281), sr, rounding_mode="floor")
-    trimmed = torch.minimum(torch.where(first64 >= 0, secs * sr, tables[2]), tables[1])
-    comp = sn.run(flat, tables[0], trimmed, max_components=max_components, max_item_samples=max_len)
-    first_h = first.cpu().numpy()                                  # synchronisation 1 (both results are ready)
-    comp_h = comp.cpu().numpy()
-    out, all_segs, per_rec = [], [], []
+    first_h = torch.empty((n,), dtype=torch.int32).pin_memory()
+    comp_h = torch.empty((n, rstride), dtype=torch.int32).pin_memory()
+    feat_plan = None
+    if want_samples:
+        f_lo, f_hi, pw, brk = (50, 11000, 2, None) if not htk else (fmin, fmax, power, mel_break)
+        feat_plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), f_lo, f_hi, brk, int(sr * segment_length),
+                          int(pw), bool(db_scale), bool(normalize))
+
+    def enqueue(lo, hi):
+        """phase 1 of recordings [lo, hi): kernels + the copy of their small results, nothing waits"""
+        first = ge.get_end_chunks(flat, tables[0, lo:hi], tables[1, lo:hi], chunk_length, max_item_samples=max_len)
+        # frames[: int(sr * length)] with length = chunk * chunk_length * 281 // sr whole seconds, or len / sr (:387-420)
+        first64 = first.to(torch.int64)
+        secs = torch.div(first64 * (chunk_length * 281), sr, rounding_mode="floor")
+        trimmed = torch.minimum(torch.where(first64 >= 0, secs * sr, tables[2, lo:hi]), tables[1, lo:hi])
+        comp = sn.run(flat, tables[0, lo:hi], trimmed, max_components=max_components, max_item_samples=max_len)
+        first_h[lo:hi].copy_(first, non_blocking=True)
+        comp_h[lo:hi].copy_(comp, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+        return done
+
+    out = [None] * n
     feat_kw = dict(fmin=fmin, fmax=fmax, pad_short_tracks=pad_short_tracks)
-    for i in range(n):
-        c = int(first_h[i])
-        length = c * chunk_length * 281 // sr if c >= 0 else int(lens[i]) / sr
-        row = comp_h[i]
-        if int(row[0]) > max_components:                           # pathological recording: redo it alone
-            n_trim = int(sr * length)
-            row = sn.run(flat, offs[i:i + 1], np.array([min(n_trim, int(lens[i]))]), max_components=65536).cpu().numpy()[0]
-        signals = _signals_from_stats(engine.collect_components(row), sr, sn.width, sn.height, sn.freqs, Signal)
-        tracks = get_tracks_from_signals([s.copy() for s in signals], length)
-        rec = {"tracks": tracks, "length": length, "signals": signals, "raw_length": int(lens[i]) / sr, "samples": None}
-        if want_samples and tracks:
-            segs, counts = segment_descriptors(int(lens[i]), sr, tracks, segment_length, segment_stride, **feat_kw)
-            segs["pcm_offset"] += int(offs[i])
-            all_segs.append(segs)
-            per_rec.append((i, counts))
-        out.append(rec)
-    if want_samples and all_segs:
-        if not htk:
-            fmin, fmax, power, mel_break = 50, 11000, 2, None
-        plan = _plan(sr, int(n_fft), int(hop_length), int(n_mels), fmin, fmax, mel_break, int(sr * segment_length),
-                     int(power), bool(db_scale), bool(normalize))
-        segs = np.concatenate(all_segs)
-        block = engine.spect_tail(plan.run(flat, segs), mean_sub, channels)
-        k = 0
-        for i, counts in per_rec:
-            samples = []
-            for cnt in counts:
-                samples.append(block[k:k + cnt])
-                k += cnt
-            out[i]["samples"] = samples
+    first_np, comp_np = first_h.numpy(), comp_h.numpy()
+
+    def finish(lo, hi):
+        """host half of recordings [lo, hi) + their classifier segments (queued, not waited for)"""
+        all_segs, per_rec = [], []
+        for i in range(lo, hi):
+            c = int(first_np[i])
+            length = c * chunk_length * 281 // sr if c >= 0 else int(lens[i]) / sr
+            row = comp_np[i]
+            if int(row[0]) > max_components:                       # pathological recording: redo it alone
+                n_trim = min(int(sr * length), int(lens[i]))
+                row = sn.run(flat, offs[i:i + 1], np.array([n_trim]), max_components=65536).cpu().numpy()[0]
+            signals = _signals_from_stats(engine.collect_components(row), sr, sn.width, sn.height, sn.freqs, Signal)
+            tracks = get_tracks_from_signals([s.copy() for s in signals], length)
+            out[i] = {"tracks": tracks, "length": length, "signals": signals, "raw_length": int(lens[i]) / sr,
+                      "samples": None}
+            if want_samples and tracks:
+                segs, counts = segment_descriptors(int(lens[i]), sr, tracks, segment_length, segment_stride, **feat_kw)
+                segs["pcm_offset"] += int(offs[i])
+                all_segs.append(segs)
+                per_rec.append((i, counts))
+        if all_segs:
+            block = engine.spect_tail(feat_plan.run(flat, np.concatenate(all_segs)), mean_sub, channels)
+            k = 0
+            for i, counts in per_rec:
+                samples = []
+                for cnt in counts:
+                    samples.append(block[k:k + cnt])
+                    k += cnt
+                out[i]["samples"] = samples
+
+    bounds = [(lo, min(lo + int(chunk), n)) for lo in range(0, n, int(chunk))]
+    pending = enqueue(*bounds[0])
+    for j, (lo, hi) in enumerate(bounds):
+        nxt = enqueue(*bounds[j + 1]) if j + 1 < len(bounds) else None     # the GPU stays busy while the host merges
+        pending.synchronize()
+        finish(lo, hi)
+        pending = nxt
     return out
 
 

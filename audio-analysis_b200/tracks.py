@@ -4,6 +4,8 @@ scalar logic, so it stays on the host; it is here so that the 
 (signal_noise before, load_samples after) form one drop-in chain.  Results are pinned against the reference's own
 functions on seeded rectangles (tests/golden/tracks.npz, tests/test_tracks_host.py).
 """
+import functools
+
 import numpy as np
 
 
@@ -15,6 +17,13 @@ def segment_overlap(first, second):
 def mel_freq(f):
     """HTK mel (src/identify_tracks.py:717-718)."""
     return 2595.0 * np.log10(1.0 + f / 700.0)
+
+
+@functools.lru_cache(maxsize=1 << 16)
+def _mel_cached(f):
+    """mel_freq as a Python float, memoised: the frequencies are FFT bin centres or small integers, a few thousand
+    distinct values, and numpy's scalar log10 is the most expensive thing the merge heuristics do."""
+    return float(mel_freq(f))
 
 
 class Signal:
@@ -36,8 +45,8 @@ class Signal:
     def _refresh_mel(self):
         # the same float64 values as the reference's numpy scalars, held as Python floats: the merge heuristics compare
         # them O(n^2) times per sweep and numpy scalar arithmetic is several times slower than float arithmetic
-        self.mel_freq_start = float(mel_freq(self.freq_start))
-        self.mel_freq_end = float(mel_freq(self.freq_end))
+        self.mel_freq_start = _mel_cached(float(self.freq_start))
+        self.mel_freq_end = _mel_cached(float(self.freq_end))
 
     # -- geometry ------------------------------------------------------------------------------------------
     @property

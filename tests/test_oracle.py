@@ -166,3 +166,54 @@ def test_signal_noise_oracle_equals_reference_fixture(golden):
         rec = synth.recording(int(g[name + "_seed"]), seconds=float(g[name + "_seconds"]))
         sig = O.signal_noise(rec, 48000)
         assert np.array_equal(np.array(sig, dtype=np.float64).reshape(-1, 4), g[name + "_signals"])
+
+
+def test_librosa_stand_ins_against_torchaudio():
+    """Independent cross-check of the restated librosa layer (librosa itself is not installable here): torchaudio ships its
+    own Slaney mel filterbank, dB conversion and STFT.  Agreement is to float32 rounding, not bit-exact (different
+    operation order), which is what pins the SEMANTICS: periodic Hann, centre zero padding, 1 + len // hop frames;
+    Slaney scale and area normalisation; amin / ref=max / top_db clamp."""
+    import os
+    import sys
+    import torch
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pytest.importorskip("torchaudio")
+    import torchaudio.functional as F
+    stubs = os.path.join(ROOT, "oracle", "stubs")
+    sys.path.insert(0, stubs)
+    saved = {k: sys.modules.pop(k) for k in list(sys.modules) if k == "librosa" or k.startswith("librosa.")}
+    try:
+        import librosa
+        from librosa import feature
+        # filters.mel (htk=False branch of get_spect, src/identify_tracks.py:229-238)
+        w = feature.filters_mel(48000, 4096, n_mels=160, fmin=50, fmax=11000)
+        fb = F.melscale_fbanks(n_freqs=2049, f_min=50.0, f_max=11000.0, n_mels=160, sample_rate=48000, norm="slaney",
+                               mel_scale="slaney").numpy().T
+        # torchaudio builds the triangles in float32, librosa in float64: 2e-7 absolute on weights of up to 0.049
+        assert w.shape == fb.shape and np.abs(w - fb).max() <= 1e-6
+        assert np.array_equal(w.argmax(axis=1), fb.argmax(axis=1))
+        # power_to_db(ref=np.max) (src/identify_tracks.py:265-266)
+        x = (np.abs(np.random.default_rng(0).standard_normal((64, 100))).astype(np.float32) ** 2) * 1e-3
+        x[3, 5] = 0.0
+        db = F.amplitude_to_DB(torch.from_numpy(x), multiplier=10.0, amin=1e-10,
+                               db_multiplier=float(np.log10(max(1e-10, x.max()))), top_db=80.0).numpy()
+        assert np.abs(db - librosa.power_to_db(x, ref=np.max)).max() <= 1e-4
+        # amplitude_to_db(ref=np.max) (src/identify_morepork.py:152): 20 log10 with amin 1e-5
+        a = np.sqrt(x)
+        dba = F.amplitude_to_DB(torch.from_numpy(a), multiplier=20.0, amin=1e-5,
+                                db_multiplier=float(np.log10(max(1e-5, a.max()))), top_db=80.0).numpy()
+        assert np.abs(dba - librosa.amplitude_to_db(a, ref=np.max)).max() <= 1e-4
+        # stft framing (periodic Hann, centre, zero padding) against torchaudio's Spectrogram
+        rec = synth.recording(3, seconds=1.0)
+        for n_fft, hop in ((4096, 281), (4800, 2400)):
+            ref = np.abs(librosa.stft(rec, n_fft=n_fft, hop_length=hop))
+            got = F.spectrogram(torch.from_numpy(rec).double(), pad=0, window=torch.hann_window(n_fft, periodic=True, dtype=torch.float64),
+                                n_fft=n_fft, hop_length=hop, win_length=n_fft, power=1.0, normalized=False, center=True,
+                                pad_mode="constant").numpy()
+            assert got.shape == ref.shape == (1 + n_fft // 2, 1 + len(rec) // hop)
+            assert np.abs(got - ref).max() <= 1e-5 * ref.max()
+    finally:
+        sys.path.remove(stubs)
+        for k in [k for k in sys.modules if k == "librosa" or k.startswith("librosa.")]:
+            sys.modules.pop(k)
+        sys.modules.update(saved)
