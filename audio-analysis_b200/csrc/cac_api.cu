@@ -17,12 +17,12 @@
 namespace cac {
 cudaError_t launch_segment_rows(const float* pcm, const cac_segment* segs, long long n, float* rows, int seg_len,
                                 int n_frames, int normalize, long long* tab, cudaStream_t st);
-cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st);
 size_t feat_smem_bytes(const FeatArgs& a);
 cudaError_t launch_features(const FeatArgs& a, int power, int db_scale, cudaStream_t st, cudaEvent_t ev0,
                             cudaEvent_t ev1);
 cudaError_t launch_normalize(const float* in, float* out, long long rows, int row_len, cudaStream_t st);
-cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power, cudaStream_t st);
+cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power,
+                               const BandTable* d_bands, const float* d_weights, cudaStream_t st);
 cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, long long item_len, unsigned* work,
                                cudaStream_t st);
 }  // namespace cac
@@ -30,8 +30,6 @@ cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, l
 using namespace cac;
 
 static thread_local std::string g_err;
-static std::atomic<uint64_t> g_next_plan_id{1};
-static uint64_t g_const_owner[64] = {0};   // plan whose band table is in __constant__ memory, per device
 
 int cac::fail(int code, const std::string& msg) {
     g_err = msg;
@@ -42,8 +40,9 @@ struct cac_plan {
     cac_params p;
     int device;
     int n_frames;
-    uint64_t id;
     MelBands mb;                     // banded filterbank (mel_bands.h), host copy
+    BandTable* d_bt = nullptr;       // the plan's own device copy of the band table and its taps (cac_mel_project_run)
+    float* d_bw = nullptr;
     int frames_per_stage, stage_half;
     float* d_wpad = nullptr;
     int* d_mstart = nullptr;
@@ -82,12 +81,7 @@ extern "C" int cac_device_count(void) {
     return n;
 }
 
-static int ensure_constants(cac_plan* plan, cudaStream_t st) {
-    if (plan->device < 64 && g_const_owner[plan->device] == plan->id) return CAC_OK;
-    CUDA_TRY(upload_bands(plan->mb.bt, plan->mb.weights.data(), (int)plan->mb.weights.size(), st));
-    if (plan->device < 64) g_const_owner[plan->device] = plan->id;
-    return CAC_OK;
-}
+extern "C" int cac_plan_destroy(cac_plan* plan);
 
 extern "C" int cac_plan_create(const cac_params* params, const float* w, int device, cac_plan** out) {
     if (!params || !w || !out) return fail(CAC_ERR_INVALID, "null argument");
@@ -105,7 +99,6 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
     cac_plan* plan = new cac_plan();
     plan->p = p;
     plan->device = device;
-    plan->id = g_next_plan_id++;
     plan->n_frames = 1 + p.segment_samples / p.hop_length;
     const int bins = 1 + p.n_fft / 2;
     const std::string berr = plan->mb.build(w, p.n_mels, bins, /*absolute=*/true);
@@ -193,6 +186,19 @@ extern "C" int cac_plan_create(const cac_params* params, const float* w, int dev
             return fail(CAC_ERR_ALLOC, "could not upload the filterbank tables");
         }
     }
+    {   // band table of cac_mel_project_run: owned by the plan (no process-wide __constant__ state)
+        cudaSetDevice(device);
+        const size_t wbytes = std::max<size_t>(plan->mb.weights.size(), 1) * sizeof(float);
+        cudaError_t e = cudaMalloc((void**)&plan->d_bt, sizeof(BandTable));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&plan->d_bw, wbytes);
+        if (e == cudaSuccess) e = cudaMemcpy(plan->d_bt, &plan->mb.bt, sizeof(BandTable), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && !plan->mb.weights.empty())
+            e = cudaMemcpy(plan->d_bw, plan->mb.weights.data(), plan->mb.weights.size() * sizeof(float), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            cac_plan_destroy(plan);
+            return fail(CAC_ERR_ALLOC, "could not upload the band table");
+        }
+    }
     *out = plan;
     return CAC_OK;
 }
@@ -204,10 +210,9 @@ extern "C" int cac_plan_destroy(cac_plan* plan) {
     for (cudaEvent_t e : plan->ev_up) cudaEventDestroy(e);
     for (cudaEvent_t e : plan->ev_done) cudaEventDestroy(e);
     if (plan->s_h2d) { cudaStreamDestroy(plan->s_h2d); cudaStreamDestroy(plan->s_comp); cudaStreamDestroy(plan->s_d2h); }
-    cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
+    cudaFree(plan->d_wpad); cudaFree(plan->d_mstart); cudaFree(plan->d_bt); cudaFree(plan->d_bw);
     cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_gwpad); cudaFree(plan->d_gmstart);
     cudaFree(plan->d_pcm); cudaFree(plan->d_pcm16); cudaFree(plan->d_segs); cudaFree(plan->d_out); cudaFree(plan->d_work);
-    if (plan->device < 64 && g_const_owner[plan->device] == plan->id) g_const_owner[plan->device] = 0;
     delete plan;
     return CAC_OK;
 }
@@ -308,8 +313,6 @@ extern "C" int cac_features_run(cac_plan* plan, const float* d_pcm, const cac_se
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(plan->device));
     if (plan->general) return features_run_general(plan, d_pcm, d_segs, n, d_out, d_work, st);
-    int rc = ensure_constants(plan, st);
-    if (rc) return rc;
     FeatArgs a{};
     a.pcm = d_pcm; a.segs = d_segs; a.out = d_out;
     a.segstat = (float2*)d_work;
@@ -465,9 +468,8 @@ extern "C" int cac_mel_project_run(cac_plan* plan, const float* d_mag, int32_t n
     if (!plan || !d_mag || !d_out || n_frames < 0) return fail(CAC_ERR_INVALID, "bad argument");
     if (n_frames == 0) return CAC_OK;
     CUDA_TRY(cudaSetDevice(plan->device));
-    int rc = ensure_constants(plan, (cudaStream_t)stream);
-    if (rc) return rc;
-    CUDA_TRY(launch_mel_project(d_mag, d_out, n_frames, plan->p.n_mels, plan->p.power, (cudaStream_t)stream));
+    CUDA_TRY(launch_mel_project(d_mag, d_out, n_frames, plan->p.n_mels, plan->p.power, plan->d_bt, plan->d_bw,
+                                (cudaStream_t)stream));
     return CAC_OK;
 }
 

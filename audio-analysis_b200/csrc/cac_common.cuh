@@ -8,7 +8,7 @@ namespace cac {
 
 constexpr int kWarp = 32;
 constexpr int kMaxMels = 512;
-constexpr int kMaxTaps = 12288;   // packed band weights kept in __constant__ memory
+constexpr int kMaxTaps = 12288;   // packed band weights of one plan (device copy owned by the plan)
 
 // Banded filterbank (one contiguous band per mel row), uploaded per plan.
 struct BandTable {

@@ -17,8 +17,6 @@
 
 namespace cac {
 
-__constant__ BandTable c_bands;
-__constant__ float c_weights[kMaxTaps];
 
 // Shared-memory carve-up of stft_mel_kernel (floats unless noted); the launcher uses the same function.
 struct FeatSmem {
@@ -398,12 +396,14 @@ __global__ void item_table_kernel(long long* tab, long long n, int seg_len, int 
 
 // ---- custommel.mel_spec on a caller-supplied magnitude matrix [bins, frames] ----------------
 __global__ void __launch_bounds__(256) mel_project_kernel(const float* __restrict__ mag, float* __restrict__ out,
-                                                          int n_frames, int n_mels, int power) {
+                                                          int n_frames, int n_mels, int power,
+                                                          const BandTable* __restrict__ bands,
+                                                          const float* __restrict__ weights) {
     const int f = blockIdx.x * 256 + threadIdx.x;
     const int m = blockIdx.y;
     if (f >= n_frames) return;
-    const int k0 = c_bands.start[m], len = c_bands.len[m];
-    const float* w = c_weights + c_bands.off[m];
+    const int k0 = bands->start[m], len = bands->len[m];
+    const float* w = weights + bands->off[m];
     float acc = 0.f;
     for (int t = 0; t < len; ++t) {
         float v = fabsf(mag[(size_t)(k0 + t) * n_frames + f]);
@@ -430,12 +430,6 @@ static void launch_db(const float* in, float* out, const unsigned* itemmax, long
         power_to_db_kernel<<<dim3((unsigned)bx, (unsigned)ny), 256, 0, st>>>(in + i0 * item_len, out + i0 * item_len,
                                                                              itemmax + i0, item_len);
     }
-}
-
-cudaError_t upload_bands(const BandTable& bt, const float* weights, int n_taps, cudaStream_t st) {
-    cudaError_t e = cudaMemcpyToSymbolAsync(c_bands, &bt, sizeof(BandTable), 0, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyToSymbolAsync(c_weights, weights, sizeof(float) * n_taps, 0, cudaMemcpyHostToDevice, st);
 }
 
 size_t feat_smem_bytes(const FeatArgs& a) {
@@ -480,9 +474,10 @@ cudaError_t launch_normalize(const float* in, float* out, long long rows, int ro
     return cudaGetLastError();
 }
 
-cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power, cudaStream_t st) {
+cudaError_t launch_mel_project(const float* mag, float* out, int n_frames, int n_mels, int power,
+                               const BandTable* d_bands, const float* d_weights, cudaStream_t st) {
     dim3 grid((n_frames + 255) / 256, n_mels);
-    mel_project_kernel<<<grid, 256, 0, st>>>(mag, out, n_frames, n_mels, power);
+    mel_project_kernel<<<grid, 256, 0, st>>>(mag, out, n_frames, n_mels, power, d_bands, d_weights);
     return cudaGetLastError();
 }
 
