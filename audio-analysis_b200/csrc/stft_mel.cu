@@ -489,3 +489,53 @@ cudaError_t launch_power_to_db(const float* in, float* out, long long n_items, l
 }
 
 }  // namespace cac
+
+// ---- cac_power_to_db_static: power_to_db without any allocation ------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-item maxima of
+// cac_power_to_db_run's caller-owned work buffer live in a file-scope device array instead: 256 KB that every GPU
+// which loads the library holds until exit.  ALL calls share the array: calls that overlap on the GPU (two streams,
+// two threads) race on it.  item_max_kernel overwrites slots [0, n_items) before power_to_db_kernel reads them, so
+// nothing has to start at zero and the previous call's contents do not matter.
+#include <mutex>
+
+#include "api_util.h"
+
+namespace cac {
+constexpr int kDbStaticDevices = 64;
+static __device__ __align__(256) unsigned g_db_static_max[CAC_POWER_TO_DB_STATIC_MAX_ITEMS];
+static unsigned* g_db_static_ptr[kDbStaticDevices] = {nullptr};   // device address of the array, per device
+static std::mutex g_db_static_mu;
+
+// In host code `g_db_static_max` is only the host-side stand-in of the symbol; its device address is looked up once
+// per device, with that device current.
+static int db_static_scratch(unsigned** out) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kDbStaticDevices) return fail(CAC_ERR_INVALID, "cac_power_to_db_static: device index out of range");
+    std::lock_guard<std::mutex> lock(g_db_static_mu);
+    if (!g_db_static_ptr[dev]) {
+        unsigned* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_db_static_max));
+        g_db_static_ptr[dev] = p;
+    }
+    *out = g_db_static_ptr[dev];
+    return CAC_OK;
+}
+}  // namespace cac
+
+extern "C" int cac_power_to_db_static(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* stream) {
+    using namespace cac;
+    if (!d_in || !d_out || n_items < 0 || item_len < 1) return fail(CAC_ERR_INVALID, "bad argument");
+    if (n_items > CAC_POWER_TO_DB_STATIC_MAX_ITEMS)
+        return fail(CAC_ERR_INVALID, "cac_power_to_db_static: n_items = " + std::to_string((long long)n_items) +
+                                         " exceeds the static scratch of " +
+                                         std::to_string(CAC_POWER_TO_DB_STATIC_MAX_ITEMS) +
+                                         " items; use cac_power_to_db_run with a caller-owned work buffer");
+    if (n_items == 0) return CAC_OK;
+    unsigned* scratch = nullptr;
+    const int rc = db_static_scratch(&scratch);
+    if (rc) return rc;
+    CUDA_TRY(launch_power_to_db(d_in, d_out, n_items, item_len, scratch, (cudaStream_t)stream));
+    return CAC_OK;
+}

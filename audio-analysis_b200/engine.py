@@ -52,6 +52,8 @@ lib.cac_features_host_pcm16.argtypes = [_vp, _vp, _i64, _vp, _i64, _vp]
 lib.cac_normalize_run.argtypes = [_vp, _vp, _i64, _i32, _vp]
 lib.cac_mel_project_run.argtypes = [_vp, _vp, _i32, _vp, _vp]
 lib.cac_power_to_db_run.argtypes = [_vp, _vp, _i64, _i64, _vp, _vp]
+lib.cac_power_to_db_static.argtypes = [_vp, _vp, _i64, _i64, _vp]
+POWER_TO_DB_STATIC_MAX_ITEMS = 65536      # CAC_POWER_TO_DB_STATIC_MAX_ITEMS
 
 lib.cac_ci_plan_create.argtypes = [_i32, _vp, _vp, ctypes.c_int, ctypes.POINTER(_vp)]
 lib.cac_ci_plan_destroy.argtypes = [_vp]
@@ -107,7 +109,7 @@ EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resampl
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_measure_fp32_tflops", "cac_plan_set_magtransform", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
-           "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run"]
+           "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run", "cac_power_to_db_static"]
 
 
 class CacError(RuntimeError):

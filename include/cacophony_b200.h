@@ -128,6 +128,16 @@ int cac_mel_project_run(cac_plan* plan, const float* d_mag, int32_t n_frames, fl
 int cac_power_to_db_run(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* d_work,
                         void* stream);
 
+/* cac_power_to_db_run without d_work and without any allocation (no cudaMalloc / cudaFree, no allocating library
+ * call): the per-item maxima go to a static device array inside the library.  It has NO counterpart in the
+ * reference; it was added for callers that cannot allocate (CUDA graph
+ * capture, tight serving loops).  Works on the CURRENT device, like cac_power_to_db_run.  n_items above
+ * CAC_POWER_TO_DB_STATIC_MAX_ITEMS is rejected with CAC_ERR_INVALID.  All calls share the one array: calls that
+ * overlap on the GPU race; serialise them (one stream) or use cac_power_to_db_run.  Results are bit-identical to
+ * cac_power_to_db_run's. */
+#define CAC_POWER_TO_DB_STATIC_MAX_ITEMS 65536
+int cac_power_to_db_static(const float* d_in, float* d_out, int64_t n_items, int64_t item_len, void* stream);
+
 /* ---- old Cacophony Index (src/cacophony_index.py) ------------------------------------------------
  * float64 throughout, like the reference (numpy.hanning * window -> scipy.fftpack.dct -> band sums). */
 typedef struct cac_ci_plan cac_ci_plan;
