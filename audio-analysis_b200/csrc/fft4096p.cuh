@@ -86,21 +86,22 @@ struct UntangleP {
     }
 };
 
-// Same contract as fft_frame (fft4096.cuh)
-template <int POWER, int K2N, bool NYQ = false>
-__device__ __forceinline__ void fft_frame_p(const float* __restrict__ se, const float* __restrict__ so, int u0,
-                                            float* __restrict__ ex, float* __restrict__ pbuf, int lane,
-                                            const float* __restrict__ lt) {
-    float2 a[64];
-    {
-        const float* pe;
-        const float* po;
-        if (u0 & 1) { pe = so + (u0 >> 1) + lane; po = se + ((u0 + 1) >> 1) + lane; }
-        else        { pe = se + (u0 >> 1) + lane; po = so + (u0 >> 1) + lane; }
-        WinLoadP<0>::run(a, pe, po, make_float2(lt[0 * 32], lt[2 * 32]), make_float2(lt[1 * 32], lt[3 * 32]));
-    }
+// The frame in two halves, so that a caller can put other work (a barrier) between them:
+// fft_frame_p_load: windowed samples -> radix-64 pass, state = the 64 complex values of the lane;
+// fft_frame_p_finish: exchange, twiddles, two radix-32 passes, untangle -> power values in pbuf.
+__device__ __forceinline__ void fft_frame_p_load(const float* __restrict__ se, const float* __restrict__ so, int u0,
+                                                 int lane, const float* __restrict__ lt, float2 (&a)[64]) {
+    const float* pe;
+    const float* po;
+    if (u0 & 1) { pe = so + (u0 >> 1) + lane; po = se + ((u0 + 1) >> 1) + lane; }
+    else        { pe = se + (u0 >> 1) + lane; po = so + (u0 >> 1) + lane; }
+    WinLoadP<0>::run(a, pe, po, make_float2(lt[0 * 32], lt[2 * 32]), make_float2(lt[1 * 32], lt[3 * 32]));
     fft_dif_c<64>(a);
+}
 
+template <int POWER, int K2N, bool NYQ = false>
+__device__ __forceinline__ void fft_frame_p_finish(const float2 (&a)[64], float* __restrict__ ex, float* __restrict__ pbuf,
+                                                   int lane, const float* __restrict__ lt) {
     float2 z0[32], z1[32];
     float2* ex2 = reinterpret_cast<float2*>(ex);
     __syncwarp();
@@ -131,6 +132,16 @@ __device__ __forceinline__ void fft_frame_p(const float* __restrict__ se, const 
             pbuf[2048] = POWER == 1 ? fabsf(x) : x * x;
         }
     }
+}
+
+// Same contract as fft_frame (fft4096.cuh)
+template <int POWER, int K2N, bool NYQ = false>
+__device__ __forceinline__ void fft_frame_p(const float* __restrict__ se, const float* __restrict__ so, int u0,
+                                            float* __restrict__ ex, float* __restrict__ pbuf, int lane,
+                                            const float* __restrict__ lt) {
+    float2 a[64];
+    fft_frame_p_load(se, so, u0, lane, lt, a);
+    fft_frame_p_finish<POWER, K2N, NYQ>(a, ex, pbuf, lane, lt);
 }
 
 }  // namespace cac

@@ -1,5 +1,6 @@
 // C-ABI of the framed-spectrum paths (include/cacophony_b200.h, cac_spec_* and helpers):
 // identify_morepork._load_sample + window loop, identify_tracks.get_end, signal_noise's STFT.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -23,13 +24,36 @@ struct cac_spec_plan {
     long long* d_wtab = nullptr;  size_t wtab_cap = 0;   // morepork window tables
     bool dft = false;             // any other frame length: direct band DFT (band_dft.cu), raw bands only
     float2* d_tw = nullptr;
+    // hop = n_fft / 2 and a raw band of at most 62 bins (identify_morepork): the band DFT as a tensor-core GEMM over
+    // non-overlapping chunks (band_gemm.cu); d_P = the chunks' partial transforms, grown on demand by cac_spec_run
+    bool gemm = false;
+    float* d_bsw = nullptr;
+    float* d_P = nullptr;         size_t P_cap = 0;
 };
 
 namespace cac {
 void band_dft_host_table(int n_fft, float2* tw);
 size_t band_dft_smem_bytes(int n_fft);
 cudaError_t launch_band_dft(const SpecArgs& a, const float2* tw, cudaStream_t st);
+bool band_gemm_supported(int n_fft, int hop, int kmin, int nbins);
+size_t band_gemm_table_floats(int hop);
+size_t band_gemm_scratch_bytes(long long total_rows);
+void band_gemm_host_table(int n_fft, int hop, int kmin, int nbins, float* out);
+cudaError_t launch_band_gemm(const SpecArgs& a, const float* d_bsw, float* d_P, cudaStream_t st);
 }  // namespace cac
+
+// the GEMM tables of a raw-band plan with hop = n_fft / 2 (no error when the shape does not qualify: the other kernels serve it)
+static int setup_band_gemm(cac_spec_plan* plan) {
+    const cac_spec_params& p = plan->p;
+    if (p.n_mels != 0 || p.bin_major || !band_gemm_supported(p.n_fft, p.hop_length, plan->kmin, plan->nbins)) return CAC_OK;
+    std::vector<float> tab(band_gemm_table_floats(p.hop_length));
+    band_gemm_host_table(p.n_fft, p.hop_length, plan->kmin, plan->nbins, tab.data());
+    cudaError_t e = cudaMalloc((void**)&plan->d_bsw, tab.size() * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(plan->d_bsw, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return fail(CAC_ERR_ALLOC, std::string("could not upload the band GEMM table: ") + cudaGetErrorString(e));
+    plan->gemm = true;
+    return CAC_OK;
+}
 
 // librosa.stft(center=True): 1 + (n + 2 (n_fft // 2) - n_fft) // hop frames (= 1 + n // hop for even n_fft)
 static long long frames_of(const cac_spec_plan* plan, long long n) {
@@ -84,6 +108,7 @@ extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* 
             delete plan;
             return fail(CAC_ERR_ALLOC, std::string("could not upload the DFT table: ") + cudaGetErrorString(e));
         }
+        if (int rc = setup_band_gemm(plan)) { cac_spec_plan_destroy(plan); return rc; }
         *out = plan;
         return CAC_OK;
     }
@@ -115,6 +140,7 @@ extern "C" int cac_spec_plan_create(const cac_spec_params* params, const float* 
         delete plan;
         return fail(CAC_ERR_ALLOC, std::string("could not upload the spectrum tables: ") + cudaGetErrorString(e));
     }
+    if (int rc = setup_band_gemm(plan)) { cac_spec_plan_destroy(plan); return rc; }
     *out = plan;
     return CAC_OK;
 }
@@ -123,7 +149,7 @@ extern "C" int cac_spec_plan_destroy(cac_spec_plan* plan) {
     if (!plan) return CAC_OK;
     cudaSetDevice(plan->device);
     cudaFree(plan->d_ltab); cudaFree(plan->d_rtab); cudaFree(plan->d_wpad); cudaFree(plan->d_mstart);
-    cudaFree(plan->d_tab); cudaFree(plan->d_wtab); cudaFree(plan->d_tw);
+    cudaFree(plan->d_tab); cudaFree(plan->d_wtab); cudaFree(plan->d_tw); cudaFree(plan->d_bsw); cudaFree(plan->d_P);
     delete plan;
     return CAC_OK;
 }
@@ -147,8 +173,13 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
     CUDA_TRY(cudaSetDevice(plan->device));
     std::vector<long long> tab(3 * (size_t)n_items + 1);          // [item_off | item_len | frame_base]
     long long total = 0;
+    // the GEMM path copies 16 bytes at a time: every recording must start on a 16-byte boundary
+    // (CAC_BAND_GEMM=0 keeps the mixed-radix / direct kernels: A/B runs and the parity test between the two paths)
+    const char* gemm_env = getenv("CAC_BAND_GEMM");
+    bool gemm = plan->gemm && !(gemm_env && gemm_env[0] == '0') && ((uintptr_t)d_pcm & 15) == 0;
     for (int64_t i = 0; i < n_items; ++i) {
         if (h_item_offset[i] < 0 || h_item_samples[i] < 0) return fail(CAC_ERR_INVALID, "negative item offset/length");
+        if (h_item_offset[i] & 3) gemm = false;
         tab[i] = h_item_offset[i];
         tab[n_items + i] = h_item_samples[i];
         tab[2 * n_items + i] = total;
@@ -183,8 +214,15 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
     a.n_groups = plan->mb.n_groups;
     a.pbuf_len = plan->mb.pbuf_len;
     for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
-    if (plan->dft) CUDA_TRY(launch_band_dft(a, plan->d_tw, st));
-    else CUDA_TRY(launch_spec4800(a, st));
+    if (gemm) {
+        rc = ensure_cap(&plan->d_P, &plan->P_cap, band_gemm_scratch_bytes(total));
+        if (rc) return rc;
+        CUDA_TRY(launch_band_gemm(a, plan->d_bsw, plan->d_P, st));
+    } else if (plan->dft) {
+        CUDA_TRY(launch_band_dft(a, plan->d_tw, st));
+    } else {
+        CUDA_TRY(launch_spec4800(a, st));
+    }
     return CAC_OK;
 }
 

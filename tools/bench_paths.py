@@ -116,7 +116,9 @@ def path_morepork(n_rec=4096, cpu=True):
     algo = pcm.numel() * 4 + out.numel() * 4
     res = {"config": "configs[2]: %d x 60 s 48 kHz recordings, morepork spectrogram + windows" % n_rec, "ms": ms,
            "recording_hours_per_s": n_rec / 60.0 / (ms * 1e-3), "algorithmic_bytes": algo,
-           "hbm_frac": algo / ms / 1e6 / hbm_peak(), "dominant_kernel": "spec4800_kernel<75>", "dtype": "f32"}
+           "hbm_frac": algo / ms / 1e6 / hbm_peak(),
+           "dominant_kernel": "spec4800_kernel<75>" if os.environ.get("CAC_BAND_GEMM", "1")[:1] == "0" else
+           "band_gemm_kernel (tcgen05.mma kind::tf32, 3-product split, FP32 accumulate in TMEM)", "dtype": "f32"}
     if cpu:
         from oracle import oracle_np as O
         t0 = time.perf_counter()

@@ -18,7 +18,10 @@ for r in csv.reader(out.splitlines()):
     elif r[0] == "Line No":
         S, I = r.index("# Samples"), r.index("Instructions Executed")
     elif r[0].isdigit() and S is not None and len(r) > I:
-        lines.append((int(r[S] or 0), int(r[I] or 0), fname, int(r[0]), r[1].strip()))
+        try:        # a source line that itself holds quotes and commas splits wrongly: skip it
+            lines.append((int(r[S] or 0), int(r[I] or 0), fname, int(r[0]), r[1].strip()))
+        except ValueError:
+            pass
 tot = sum(x[0] for x in lines) or 1
 tot_i = sum(x[1] for x in lines) or 1
 print("samples", tot, "warp instructions", tot_i)
