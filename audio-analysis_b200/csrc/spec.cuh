@@ -26,6 +26,12 @@ struct SpecArgs {
     // values are not stored; chunk_mm[item * chunk_stride + frame / chunk_frames] = {min, max} (float bits, values >= 0)
     uint2* chunk_mm;
     int chunk_frames, chunk_stride;
+    // get_end in two phases (exact: a chunk whose first frame already holds two different values is not constant).
+    // chunk_probe = 1: only frame c * chunk_frames of every chunk slot (item, c) is transformed, global index = item *
+    // chunk_stride + c.  chunk_list: only the frames of the listed (item, chunk) pairs, *chunk_list_n of them.
+    int chunk_probe;
+    const int2* chunk_list;
+    const int* chunk_list_n;
     // per-plan tables
     const float2* ltab;            // per-lane twiddle / window constants
     const float2* rtab;            // per-round untangle twiddles
@@ -53,6 +59,9 @@ cudaError_t launch_scale_by_max(float* data, long long n, const float* gmax, cud
 cudaError_t launch_get_end_prep(const long long* d_item_off, const long long* d_item_len, int n_items, int n_fft, int hop,
                                 long long max_item_samples, long long* tab, uint2* mm, int chunk_stride, int* out,
                                 cudaStream_t st);
+// after the probe: the examined chunks whose probe frame was constant go on the list (their full evaluation follows)
+cudaError_t launch_get_end_select(const long long* tab, int n_items, const uint2* mm, int chunk_stride, int chunk_frames,
+                                  int2* list, int* list_n, cudaStream_t st);
 cudaError_t launch_get_end_scan(const long long* tab, int n_items, const uint2* mm, int chunk_stride, int chunk_frames,
                                 int* out, cudaStream_t st);
 

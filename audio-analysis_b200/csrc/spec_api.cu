@@ -265,7 +265,7 @@ extern "C" int cac_morepork_windows_run(cac_spec_plan* plan, const float* d_spec
 
 // ---- identify_tracks.get_end for a batch (device item tables, chunk scan on the device) -----------------------------
 namespace {
-struct GetEndLayout { size_t tab, mm, total; int chunk_stride; };
+struct GetEndLayout { size_t tab, mm, list, list_n, total; int chunk_stride; };
 GetEndLayout get_end_layout(const cac_spec_plan* plan, int64_t n_items, int64_t max_item_samples, int chunk_frames) {
     GetEndLayout L;
     const long long max_frames = frames_of(plan, max_item_samples);
@@ -273,6 +273,8 @@ GetEndLayout get_end_layout(const cac_spec_plan* plan, int64_t n_items, int64_t 
     size_t o = 0;
     L.tab = o; o += ((3 * (size_t)n_items + 1) * sizeof(long long) + 255) / 256 * 256;
     L.mm = o; o += ((size_t)n_items * L.chunk_stride * sizeof(uint2) + 255) / 256 * 256;
+    L.list = o; o += ((size_t)n_items * L.chunk_stride * sizeof(int2) + 255) / 256 * 256;    // candidate (item, chunk) pairs
+    L.list_n = o; o += 256;
     L.total = o;
     return L;
 }
@@ -321,6 +323,15 @@ extern "C" int cac_get_end_run(cac_spec_plan* plan, const float* d_pcm, const in
     a.chunk_mm = mm;
     a.chunk_frames = chunk_frames;
     a.chunk_stride = L.chunk_stride;
+    // Phase 1: ONE frame per chunk.  A chunk whose first frame already holds two different mel values cannot be the
+    // constant chunk the reference looks for (np.amax(data) == np.amin(data), :408); only the chunks whose first frame is
+    // constant - digital silence, in practice - are transformed in full (phase 2).  Same values, same answer, 1 / 170 of
+    // the frames for a recording without a silent tail.
+    int2* list = reinterpret_cast<int2*>((char*)d_work + L.list);
+    int* list_n = reinterpret_cast<int*>((char*)d_work + L.list_n);
+    CUDA_TRY(cudaMemsetAsync(list_n, 0, sizeof(int), st));
+    a.chunk_probe = 1;
+    a.n_frames_total = (long long)n_items * L.chunk_stride;
     a.ltab = plan->d_ltab;
     a.rtab = plan->d_rtab;
     a.wpad = plan->d_wpad;
@@ -329,6 +340,12 @@ extern "C" int cac_get_end_run(cac_spec_plan* plan, const float* d_pcm, const in
     a.n_groups = plan->mb.n_groups;
     a.pbuf_len = plan->mb.pbuf_len;
     for (int g = 0; g < 16; ++g) { a.gmax_taps[g] = plan->mb.gmax[g]; a.goff[g] = plan->mb.goff[g]; }
+    CUDA_TRY(launch_spec4800(a, st));
+    CUDA_TRY(launch_get_end_select(tab, (int)n_items, mm, L.chunk_stride, chunk_frames, list, list_n, st));
+    a.chunk_probe = 0;
+    a.chunk_list = list;
+    a.chunk_list_n = list_n;
+    a.n_frames_total = -1;                    // on the device: *list_n chunks
     CUDA_TRY(launch_spec4800(a, st));
     CUDA_TRY(launch_get_end_scan(tab, (int)n_items, mm, L.chunk_stride, chunk_frames, d_out, st));
     return CAC_OK;

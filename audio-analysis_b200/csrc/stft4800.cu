@@ -148,10 +148,21 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
             if (a.frame_base[mid] <= g) lo = mid; else hi = mid - 1;
         }
     }
-    const long long n_total = a.n_frames_total >= 0 ? a.n_frames_total : a.frame_base[a.n_items];
+    const long long n_total = a.chunk_list ? (long long)(*a.chunk_list_n) * a.chunk_frames
+                            : a.chunk_probe ? (long long)a.n_items * a.chunk_stride
+                            : a.n_frames_total >= 0 ? a.n_frames_total : a.frame_base[a.n_items];
 #pragma unroll 1
     for (long long g = (long long)blockIdx.x * kWarps48 + warp; g < n_total; g += stride) {
-        if (kWalk) {
+        int fsel = -1;                                                    // frame within the item when a chunk mode picks it
+        if (a.chunk_list) {
+            const int e = (int)(g / a.chunk_frames);
+            const int2 ic = a.chunk_list[e];
+            lo = ic.x;
+            fsel = ic.y * a.chunk_frames + (int)(g - (long long)e * a.chunk_frames);
+        } else if (a.chunk_probe) {
+            lo = (int)(g / a.chunk_stride);
+            fsel = (int)(g - (long long)lo * a.chunk_stride) * a.chunk_frames;
+        } else if (kWalk) {
             while (a.frame_base[lo + 1] <= g) ++lo;           // g < n_frames_total = frame_base[n_items]: stops in range
         } else {
             lo = 0;
@@ -162,8 +173,9 @@ __global__ void __launch_bounds__(kWarps48 * 32, 1) spec4800_kernel(const SpecAr
             }
         }
         const long long fbase = a.frame_base[lo];
-        const int f = (int)(g - fbase);
+        const int f = fsel >= 0 ? fsel : (int)(g - fbase);
         const int nfi = (int)(a.frame_base[lo + 1] - fbase);
+        if (a.chunk_probe && (long long)f + a.chunk_frames >= nfi) continue;   // the reference's loop never looks at that chunk
         const long long n = a.item_len[lo];
         const long long t0 = (long long)f * a.hop - kHalf;                // centre = True
         const float* p = a.pcm + a.item_off[lo] + t0;
@@ -391,6 +403,17 @@ __global__ void get_end_prep_kernel(const long long* __restrict__ off, const lon
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = -1;
 }
 
+__global__ void get_end_select_kernel(const long long* __restrict__ tab, int n, const uint2* __restrict__ mm, int chunk_stride,
+                                      int chunk_frames, int2* __restrict__ list, int* __restrict__ list_n) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)n * chunk_stride) return;
+    const int i = (int)(idx / chunk_stride), c = (int)(idx - (long long)i * chunk_stride);
+    const long long nf = tab[2 * n + i + 1] - tab[2 * n + i];
+    if ((long long)(c + 1) * chunk_frames >= nf) return;
+    const uint2 v = mm[idx];
+    if (v.x == v.y) list[atomicAdd(list_n, 1)] = make_int2(i, c);
+}
+
 // the reference's loop (src/identify_tracks.py:406-412): chunks [c L, (c + 1) L) while (c + 1) L < n_frames
 __global__ void get_end_scan_kernel(const long long* __restrict__ tab, int n, const uint2* __restrict__ mm, int chunk_stride,
                                     int chunk_frames, int* __restrict__ out) {
@@ -469,6 +492,14 @@ cudaError_t launch_get_end_prep(const long long* d_item_off, const long long* d_
     const unsigned blocks = (unsigned)std::min<long long>(std::max<long long>((cells + 255) / 256, 1), 1024);
     get_end_prep_kernel<<<blocks, 256, 0, st>>>(d_item_off, d_item_len, n_items, n_fft, hop, max_item_samples, tab, mm,
                                                 chunk_stride, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_get_end_select(const long long* tab, int n_items, const uint2* mm, int chunk_stride, int chunk_frames,
+                                  int2* list, int* list_n, cudaStream_t st) {
+    const long long cells = (long long)n_items * chunk_stride;
+    get_end_select_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(tab, n_items, mm, chunk_stride, chunk_frames, list,
+                                                                           list_n);
     return cudaGetLastError();
 }
 

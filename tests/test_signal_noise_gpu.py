@@ -181,3 +181,22 @@ def test_get_end_batch_equals_get_end(engine):
     assert T.get_end_batch(recs, 48000) == want
     assert [T.get_end(r, 48000) for r in recs] == want
     assert T.get_end_batch([], 48000) == []
+
+
+def test_get_end_probe_and_full_evaluation_agree_with_the_reference_loop(engine):
+    """cac_get_end_run transforms ONE frame per chunk first and only the chunks whose first frame is constant in full.
+    Cases that separate the two phases: a silent gap that covers a whole chunk in the MIDDLE of a recording (the reference
+    returns there), a gap that covers a chunk's first frame but not the whole chunk (candidate after the probe, rejected
+    by the full evaluation), silence that starts inside a chunk, a recording of silence only, one shorter than a chunk."""
+    from audio_analysis_b200 import identify_tracks as T
+    sr, hop, L = 48000, 281, 48000 // 281                 # 170 frames per chunk = 47,770 samples
+    base = [synth.recording(40 + i, seconds=9.0) for i in range(4)]
+    a = base[0].copy(); a[3 * L * hop - 3000: 5 * L * hop + 3000] = 0.0           # chunks 3 and 4 fully silent (plus margins)
+    b = base[1].copy(); b[2 * L * hop - 3000: 2 * L * hop + 9000] = 0.0           # only the first frames of chunk 2
+    c = base[2].copy(); c[4 * L * hop + 20000:] = 0.0                             # silence starts inside chunk 4
+    d = base[3].copy(); d[: 2 * L * hop + 4000] = 0.0                             # silent from the start for two chunks
+    recs = [a, b, c, d, np.zeros(sr * 4, np.float32), synth.recording(44, seconds=0.9), base[0]]
+    want = [O.get_end(r, sr) for r in recs]
+    assert want[0] == 3 * L * hop // sr and want[1] == len(b) / sr and want[3] == 0
+    assert T.get_end_batch(recs, sr) == want
+    assert [T.get_end(r, sr) for r in recs] == want
