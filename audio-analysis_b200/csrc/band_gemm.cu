@@ -374,16 +374,24 @@ __global__ void __launch_bounds__(256) band_frames_kernel(const float* __restric
                                                           int n_items, long long total_rows, int kmin, int nbins, int power,
                                                           float* __restrict__ out, float* gmax) {
     __shared__ float smax[8];
+    __shared__ int s_lo;
     const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (threadIdx.x == 0) {                    // the item of the block's first frame: one search per block, the threads walk on
+        const long long g0 = ((long long)blockIdx.x * 256) / nbins;
+        int lo = 0, hi = n_items - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (frame_base[mid] <= g0) lo = mid; else hi = mid - 1;
+        }
+        s_lo = lo;
+    }
+    __syncthreads();
     float mag = 0.f;
     if (idx < total_rows * nbins) {
         const long long g = idx / nbins;
         const int b = (int)(idx - g * nbins);
-        int lo = 0, hi = n_items - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (frame_base[mid] <= g) lo = mid; else hi = mid - 1;
-        }
+        int lo = s_lo;
+        while (frame_base[lo + 1] <= g) ++lo;                          // g < total_rows = frame_base[n_items]
         const bool first = frame_base[lo] == g;
         const float* cur = P + (size_t)g * kBgN + 2 * b;               // columns 2 j, 2 j + 1 = bin kmin - 1 + j; j = b, b + 1, b + 2
         float xr[3], xi[3];
