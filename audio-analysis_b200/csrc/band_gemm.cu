@@ -16,7 +16,7 @@
 // lo = x - hi (exact in FP32); three products hi.hi + lo.hi + hi.lo accumulate in FP32 in TMEM, the dropped lo.lo term
 // and the TF32 rounding of lo are ~2^-21 relative.  The tensor core adds into its FP32 accumulator with truncation:
 // over the 900 accumulations of a whole chunk (hop 2400) that is a systematic -1.7e-5 relative shrink (measured,
-// profiles/r3_experiments.md).  So the accumulator is restarted every kBgSegKb k-blocks (12 accumulations) and the
+// profiles/r3_experiments.md).  So the accumulator is restarted every kBgSegKb k-blocks (18 accumulations) and the
 // segments are summed in FP32 registers with round-to-nearest by the epilogue warps, which own a whole 128-column row
 // each (176 registers through setmaxnreg, taken from the producer / MMA warps).
 //
@@ -29,6 +29,7 @@
 //   warps 12-19 epilogue: tcgen05.ld of every finished segment accumulator (256 x 128, double-buffered: all 512 TMEM
 //               columns), running sums in registers, P rows to global memory after the tile's last segment
 // band_frames_kernel then forms the frames (sum of two P rows, Hann taps, magnitude).
+#include <cuda.h>
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -59,7 +60,7 @@ constexpr int kBgStages = 4;
 constexpr int kBgProducerWarps = 8;
 constexpr int kBgEpiWarp0 = 12, kBgEpiWarps = 8;                      // warps 8-11: B loader, MMA issuer, two spare (warpgroup-aligned roles)
 constexpr int kBgThreads = (kBgEpiWarp0 + kBgEpiWarps) * 32;          // 640
-constexpr int kBgSegKb = 2;               // k-blocks per accumulation segment (12 MMA accumulations; see "Precision")
+constexpr int kBgSegKb = 3;               // k-blocks per accumulation segment (18 MMA accumulations; see "Precision")
 // setmaxnreg: the kernel starts with 96 registers per thread (640 threads); the producer warpgroups and the MMA warpgroup
 // release what the two epilogue warpgroups take (only RELEASED registers can be taken): 256 (96 - 56) + 128 (96 - 32) =
 // 18,432 = 256 (168 - 96)
@@ -73,7 +74,7 @@ constexpr int kBgTmemCols = 512;                                      // 2 accum
 struct BgSmem {                                                       // after the stages
     const float* row_ptr[2][kBgM];
     int row_len[2][kBgM];
-    unsigned long long full[kBgStages], empty[kBgStages], acc_full[2], acc_empty[2];
+    unsigned long long landed[kBgStages], full[kBgStages], empty[kBgStages], acc_full[2], acc_empty[2];
     unsigned tmem_base;
 };
 constexpr size_t kBgSmemBytes = (size_t)kBgStages * kBgStageBytes + sizeof(BgSmem);
@@ -123,6 +124,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// one box of a 2-D tensor map (cuTensorMapEncodeTiled) -> shared memory, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, void* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+                 : "memory");
+}
 __device__ __forceinline__ void cp_async16_zfill(void* dst, const void* src, int src_bytes) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
 }
@@ -159,8 +167,13 @@ constexpr unsigned kBgIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(k
 // byte offset of the 16-byte chunk c (0..3) of row r in a 64-byte-swizzled tile (Swizzle<2,4,3>: chunk ^= (r >> 1) & 3)
 __device__ __host__ __forceinline__ int sw64_offset(int r, int c) { return r * 64 + ((c ^ ((r >> 1) & 3)) << 4); }
 
+// kTma = false: any batch whose recordings start on 16-byte boundaries; rows = chunks 0 .. frames - 1 of every recording
+//                (the last one partial or empty), fetched by the producer warps with cp.async through a per-tile row table.
+// kTma = true:  equally long recordings of a whole number of hops, back to back: the buffer IS a [chunks x hop] matrix and
+//                ONE lane fetches a whole 256-row k-block per TMA instruction (a_map); the producer warps only convert.
+template <bool kTma>
 __global__ void __launch_bounds__(kBgThreads, 1)
-band_gemm_kernel(const float* __restrict__ pcm, const long long* __restrict__ item_off, const long long* __restrict__ item_len,
+band_gemm_kernel(const __grid_constant__ CUtensorMap a_map, const float* __restrict__ pcm, const long long* __restrict__ item_off, const long long* __restrict__ item_len,
                  const long long* __restrict__ frame_base, int n_items, long long total_rows, int hop,
                  const float* __restrict__ bsw, float* __restrict__ P) {
     // no static shared memory in this kernel: the dynamic window starts at its declared alignment.  Plain indexing of the
@@ -174,7 +187,11 @@ band_gemm_kernel(const float* __restrict__ pcm, const long long* __restrict__ it
     const long long n_tiles = (total_rows + kBgM - 1) / kBgM;
 
     if (tid == 0) {
-        for (int s = 0; s < kBgStages; ++s) { mbar_init(&S.full[s], kBgProducerWarps + 1); mbar_init(&S.empty[s], 1); }
+        for (int s = 0; s < kBgStages; ++s) {
+            mbar_init(&S.landed[s], 1);
+            mbar_init(&S.full[s], (kTma ? kBgProducerWarps / 2 : kBgProducerWarps) + 1);
+            mbar_init(&S.empty[s], 1);
+        }
         for (int a = 0; a < 2; ++a) { mbar_init(&S.acc_full[a], 1); mbar_init(&S.acc_empty[a], kBgEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -188,8 +205,47 @@ band_gemm_kernel(const float* __restrict__ pcm, const long long* __restrict__ it
     tc_fence_after();
     const unsigned tmem = S.tmem_base;
     const int n_seg = (n_kb + kBgSegKb - 1) / kBgSegKb;
-    if (warp < kBgProducerWarps) {
-        // ===== A producers: thread owns chunk c of rows r0 + 64 i =====
+    if (kTma && warp < kBgProducerWarps) {
+        // ===== converters (TMA mode): the lo operand of the landed samples, lo = x - (x with the low 13 mantissa bits cleared).
+        // The hi operand is the raw sample as it landed: the MMA reads the top 19 bits of an FP32 operand and ignores the
+        // rest (measured: rewriting the truncated value changes no bit of the result).  Team warp / 4 takes every other
+        // k-block, so a team has two k-block times for its wait -> LDS -> STS -> fence -> arrive chain.  Thread owns chunk
+        // c of the rows r0 + 32 i. =====
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kBgRegsProd));
+        const int team = tid >> 7, t = tid & 127;
+        const int c = t & 3, r0 = t >> 2;
+        const int soff0 = sw64_offset(r0, c);                              // + 2048 i: (row >> 1) & 3 does not depend on i
+        long long n = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+            for (int kb = 0; kb < n_kb; ++kb, ++n) {
+                if ((int)(n & 1) != team) continue;
+                const int st = (int)(n & (kBgStages - 1));
+                mbar_wait_warp(&S.landed[st], (unsigned)((n / kBgStages) & 1), lane);
+                if (t == 0) BG_TRACE(0, (int)n);
+                const unsigned char* a_hi = stages + (size_t)st * kBgStageBytes + soff0;
+                unsigned char* a_lo = stages + (size_t)st * kBgStageBytes + kBgABytes + soff0;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    float4 v[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const float4*>(a_hi + 2048 * (4 * half + i));
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float4 l;
+                        l.x = v[i].x - __uint_as_float(__float_as_uint(v[i].x) & 0xffffe000u);
+                        l.y = v[i].y - __uint_as_float(__float_as_uint(v[i].y) & 0xffffe000u);
+                        l.z = v[i].z - __uint_as_float(__float_as_uint(v[i].z) & 0xffffe000u);
+                        l.w = v[i].w - __uint_as_float(__float_as_uint(v[i].w) & 0xffffe000u);
+                        *reinterpret_cast<float4*>(a_lo + 2048 * (4 * half + i)) = l;
+                    }
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.full[st]);
+                if (t == 0) BG_TRACE(1, (int)n);
+            }
+    } else if (warp < kBgProducerWarps) {
+        // ===== A producers (cp.async mode): thread owns chunk c of rows r0 + 64 i =====
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kBgRegsProd));
         const int c = tid & 3, r0 = tid >> 2;
         int soff[4];
@@ -270,14 +326,18 @@ band_gemm_kernel(const float* __restrict__ pcm, const long long* __restrict__ it
     } else if (warp < kBgEpiWarp0) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kBgRegsLow));
         if (warp == 8 && lane == 0) {
-            // ===== B loader: one bulk copy of the k-block's pre-swizzled [hi | lo] tile per stage =====
+            // ===== loader: one bulk copy of the k-block's pre-swizzled B tile [hi | lo] per stage (and the A box in TMA mode) =====
             {
             long long issued = 0;
             for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
                 for (int kb = 0; kb < n_kb; ++kb, ++issued) {
                     const int st = (int)(issued % kBgStages);
-                    mbar_wait_relaxed(&S.empty[st], (unsigned)(((issued / kBgStages) & 1) ^ 1), 100);
+                    mbar_wait_relaxed(&S.empty[st], (unsigned)(((issued / kBgStages) & 1) ^ 1), 32);
                     BG_TRACE(5, (int)issued);
+                    if (kTma) {                // the whole A k-block of the tile: 256 chunk rows x 16 samples, 64-byte swizzle,
+                        mbar_arrive_expect_tx(&S.landed[st], kBgABytes);     // rows past the end of the buffer arrive as zeros
+                        tma_load_2d(stages + (size_t)st * kBgStageBytes, &a_map, kb * kBgK, (int)(tile * kBgM), &S.landed[st]);
+                    }
                     mbar_arrive_expect_tx(&S.full[st], 2 * kBgBBytes);
                     bulk_g2s(stages + (size_t)st * kBgStageBytes + 2 * kBgABytes, bsw + (size_t)kb * (2 * kBgBBytes / 4),
                              2 * kBgBBytes, &S.full[st]);
@@ -420,6 +480,48 @@ __global__ void __launch_bounds__(256) band_frames_kernel(const float* __restric
     }
 }
 
+// The same for the TMA form's row numbering: item i owns the chunk rows [i C, i C + C) of P and the frames [i (C + 1),
+// (i + 1) (C + 1)); frame f = chunk f - 1 (none for f = 0) followed by chunk f (all zeros for f = C: centre padding).
+__global__ void __launch_bounds__(256) band_frames_uniform_kernel(const float* __restrict__ P, int chunks_per_item,
+                                                                  long long total_frames, int kmin, int nbins, int power,
+                                                                  float* __restrict__ out, float* gmax) {
+    __shared__ float smax[8];
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    float mag = 0.f;
+    if (idx < total_frames * nbins) {
+        const long long g = idx / nbins;
+        const int b = (int)(idx - g * nbins);
+        const long long item = g / (chunks_per_item + 1);
+        const int f = (int)(g - item * (chunks_per_item + 1));
+        const float* cur = P + (size_t)(item * chunks_per_item + f) * kBgN + 2 * b;
+        const bool has_prev = f > 0, has_cur = f < chunks_per_item;
+        float xr[3], xi[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const float s = ((kmin - 1 + b + j) & 1) ? -1.f : 1.f;
+            float pr = 0.f, pi = 0.f, cr = 0.f, ci = 0.f;
+            if (has_prev) { pr = cur[2 * j - kBgN]; pi = cur[2 * j + 1 - kBgN]; }
+            if (has_cur) { cr = cur[2 * j]; ci = cur[2 * j + 1]; }
+            xr[j] = fmaf(s, cr, pr);
+            xi[j] = fmaf(s, ci, pi);
+        }
+        const float wr = 0.5f * xr[1] - 0.25f * (xr[0] + xr[2]);
+        const float wi = 0.5f * xi[1] - 0.25f * (xi[0] + xi[2]);
+        mag = fmaf(wr, wr, wi * wi);
+        if (power == 1) mag = sqrtf(mag);
+        out[idx] = mag;
+    }
+    if (gmax) {
+        float m = warp_max(mag);
+        if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; ++w) m = fmaxf(m, smax[w]);
+            atomicMax(reinterpret_cast<unsigned*>(gmax), __float_as_uint(m));
+        }
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------------------------
 bool band_gemm_supported(int n_fft, int hop, int kmin, int nbins) {
     return n_fft == 2 * hop && hop % kBgK == 0 && hop / kBgK >= kBgStages && kmin >= 1 && nbins + 2 <= kBgN / 2 &&
@@ -428,7 +530,7 @@ bool band_gemm_supported(int n_fft, int hop, int kmin, int nbins) {
 size_t band_gemm_table_floats(int hop) { return (size_t)(hop / kBgK) * 2 * (kBgBBytes / 4); }
 size_t band_gemm_scratch_bytes(long long total_rows) {
     const long long tiles = (total_rows + kBgM - 1) / kBgM;
-    return (size_t)tiles * kBgM * kBgN * sizeof(float);
+    return (size_t)(tiles * kBgM + 1) * kBgN * sizeof(float);        // + 1: the uniform frames kernel forms (never reads) an address one row on
 }
 
 // B, k-block by k-block, [hi | lo], each a [128 columns of P][16 samples] K-major tile in the 64-byte swizzle the MMA
@@ -459,22 +561,71 @@ void band_gemm_host_table(int n_fft, int hop, int kmin, int nbins, float* out) {
     }
 }
 
-cudaError_t launch_band_gemm(const SpecArgs& a, const float* d_bsw, float* d_P, cudaStream_t st) {
-    static bool attr_set[64] = {false};
+// The PCM buffer as a [chunks x hop] row-major FP32 matrix, boxes of 256 rows x 16 samples, 64-byte swizzle.
+// cuTensorMapEncodeTiled comes from the driver through the runtime's entry-point query (no link against libcuda).
+static cudaError_t encode_a_map(const float* base, long long total_chunks, int hop, CUtensorMap* map) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess) return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)hop, (cuuint64_t)total_chunks};
+    const cuuint64_t strides[1] = {(cuuint64_t)hop * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)kBgK, (cuuint32_t)kBgM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+template <bool kTma>
+static cudaError_t set_smem_attr() {
+    static bool done[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && done[dev]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(band_gemm_kernel<kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBgSmemBytes);
+    if (e == cudaSuccess && dev < 64) done[dev] = true;
+    return e;
+}
+
+// uniform_chunks > 0: the recordings are uniform_chunks * hop samples each and lie back to back from a.pcm + item 0's offset
+// (checked by the caller, which passes that address as `base`): the TMA form.  Otherwise the cp.async form.
+cudaError_t launch_band_gemm(const SpecArgs& a, const float* base, int uniform_chunks, const float* d_bsw, float* d_P,
+                             cudaStream_t st) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
-    if (dev < 64 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(band_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBgSmemBytes);
-        if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
-    }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    alignas(64) CUtensorMap a_map;
+    memset(&a_map, 0, sizeof(a_map));
+    if (uniform_chunks > 0) {
+        const long long rows = (long long)a.n_items * uniform_chunks, frames = (long long)a.n_items * (uniform_chunks + 1);
+        cudaError_t e = set_smem_attr<true>();
+        if (e == cudaSuccess) e = encode_a_map(base, rows, a.hop, &a_map);
+        if (e != cudaSuccess) return e;
+        const long long tiles = (rows + kBgM - 1) / kBgM;
+        band_gemm_kernel<true><<<(unsigned)(tiles < sms ? tiles : sms), kBgThreads, kBgSmemBytes, st>>>(
+            a_map, nullptr, nullptr, nullptr, nullptr, 0, rows, a.hop, d_bsw, d_P);
+        const long long cells = frames * a.nbins;
+        band_frames_uniform_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(d_P, uniform_chunks, frames, a.kmin, a.nbins,
+                                                                                    a.power, a.out, a.gmax);
+        return cudaGetLastError();
+    }
     const long long rows = a.n_frames_total;
     if (rows < 1) return cudaSuccess;
+    cudaError_t e = set_smem_attr<false>();
+    if (e != cudaSuccess) return e;
     const long long tiles = (rows + kBgM - 1) / kBgM;
-    const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-    band_gemm_kernel<<<grid, kBgThreads, kBgSmemBytes, st>>>(a.pcm, a.item_off, a.item_len, a.frame_base, a.n_items, rows, a.hop,
-                                                            d_bsw, d_P);
+    band_gemm_kernel<false><<<(unsigned)(tiles < sms ? tiles : sms), kBgThreads, kBgSmemBytes, st>>>(
+        a_map, a.pcm, a.item_off, a.item_len, a.frame_base, a.n_items, rows, a.hop, d_bsw, d_P);
     const long long cells = rows * a.nbins;
     band_frames_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(d_P, a.frame_base, a.n_items, rows, a.kmin, a.nbins,
                                                                         a.power, a.out, a.gmax);

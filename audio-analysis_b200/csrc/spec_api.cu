@@ -39,7 +39,8 @@ bool band_gemm_supported(int n_fft, int hop, int kmin, int nbins);
 size_t band_gemm_table_floats(int hop);
 size_t band_gemm_scratch_bytes(long long total_rows);
 void band_gemm_host_table(int n_fft, int hop, int kmin, int nbins, float* out);
-cudaError_t launch_band_gemm(const SpecArgs& a, const float* d_bsw, float* d_P, cudaStream_t st);
+cudaError_t launch_band_gemm(const SpecArgs& a, const float* base, int uniform_chunks, const float* d_bsw, float* d_P,
+                             cudaStream_t st);
 }  // namespace cac
 
 // the GEMM tables of a raw-band plan with hop = n_fft / 2 (no error when the shape does not qualify: the other kernels serve it)
@@ -177,9 +178,13 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
     // (CAC_BAND_GEMM=0 keeps the mixed-radix / direct kernels: A/B runs and the parity test between the two paths)
     const char* gemm_env = getenv("CAC_BAND_GEMM");
     bool gemm = plan->gemm && !(gemm_env && gemm_env[0] == '0') && ((uintptr_t)d_pcm & 15) == 0;
+    // uniform batch (equal lengths, a whole number of hops, back to back): the GEMM reads it through one TMA tensor map
+    const long long len0 = h_item_samples[0], hop_l = plan->p.hop_length;
+    bool uniform = len0 >= hop_l && len0 % hop_l == 0 && len0 / hop_l < (1LL << 30);
     for (int64_t i = 0; i < n_items; ++i) {
         if (h_item_offset[i] < 0 || h_item_samples[i] < 0) return fail(CAC_ERR_INVALID, "negative item offset/length");
         if (h_item_offset[i] & 3) gemm = false;
+        if (h_item_samples[i] != len0 || h_item_offset[i] != h_item_offset[0] + i * len0) uniform = false;
         tab[i] = h_item_offset[i];
         tab[n_items + i] = h_item_samples[i];
         tab[2 * n_items + i] = total;
@@ -217,7 +222,7 @@ extern "C" int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64
     if (gemm) {
         rc = ensure_cap(&plan->d_P, &plan->P_cap, band_gemm_scratch_bytes(total));
         if (rc) return rc;
-        CUDA_TRY(launch_band_gemm(a, plan->d_bsw, plan->d_P, st));
+        CUDA_TRY(launch_band_gemm(a, d_pcm + h_item_offset[0], uniform ? (int)(len0 / hop_l) : 0, plan->d_bsw, plan->d_P, st));
     } else if (plan->dft) {
         CUDA_TRY(launch_band_dft(a, plan->d_tw, st));
     } else {
