@@ -14,11 +14,18 @@ sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, "gpurun_out")
 SR = 48000
 LENS = [int(SR * 3.3) + 7, SR * 60, 1200, 2400 * 5, 4801, SR * 11 + 1234]   # ragged, with and without a partial chunk
+if os.environ.get("CAC_DBG_UNIFORM"):                        # e.g. 600: a uniform batch of that many 40-second recordings (TMA form)
+    LENS = [2400 * 800] * int(os.environ["CAC_DBG_UNIFORM"])
 
 
 def recordings():
     from audio_analysis_b200 import synth
-    recs = [synth.recording(300 + i, seconds=n / SR + 0.01)[:n] for i, n in enumerate(LENS)]
+    pool = {}
+    recs = []
+    for i, n in enumerate(LENS):
+        if (i % 8, n) not in pool:
+            pool[(i % 8, n)] = synth.recording(300 + i % 8, seconds=n / SR + 0.01)[:n]
+        recs.append(pool[(i % 8, n)])
     offs, pos = [], 0
     for r in recs:
         offs.append(pos)
@@ -75,7 +82,7 @@ def trace():
     rc = engine.lib.cac_debug_band_gemm_trace(buf.ctypes.data_as(ctypes.c_void_p))
     assert rc == 0, rc
     t0 = buf[0, 0]
-    names = ["P data landed", "P arrived full", "P issued kb+3", "M full seen", "M committed", "B issue"]
+    names = ["landed seen", "conv arrived", "(cp) issued +3", "M full seen", "M committed", "L empty seen"]
     print("kb   " + "  ".join("%-14s" % n for n in names))
     for kb in list(range(0, 24)) + list(range(100, 108)):
         print("%3d  " % kb + "  ".join("%-14d" % (buf[r, kb] - t0) for r in range(6)))
@@ -83,8 +90,14 @@ def trace():
     print("M commit period over kb 20..140: mean %.0f min %d max %d clk" % (d.mean(), d.min(), d.max()))
     for r, n in enumerate(names):
         print("%-16s mean period %.0f" % (n, np.diff(buf[r, 20:140]).mean()))
-    print("mean (M full seen - P arrived full) %.0f;  (P data landed(kb) - P issued(kb-3)) %.0f;  (M committed(kb) - M full seen(kb)) %.0f" %
-          ((buf[3, 20:140] - buf[1, 20:140]).mean(), (buf[0, 23:140] - buf[2, 20:137]).mean(), (buf[4, 20:140] - buf[3, 20:140]).mean()))
+    sl = slice(20, 140)
+    print("means: landed - empty seen %.0f | arrived - landed %.0f | M full seen - arrived %.0f | commit - full seen %.0f | "
+          "next full seen - commit %.0f | last team warp arrived - first %.0f | M full seen - last arrive %.0f" %
+          ((buf[0, sl] - buf[5, sl]).mean(), (buf[1, sl] - buf[0, sl]).mean(),
+           (buf[3, sl] - buf[1, sl]).mean(), (buf[4, sl] - buf[3, sl]).mean(),
+           (buf[3, 21:141] - buf[4, sl]).mean(), (buf[6, sl] - buf[1, sl]).mean(), (buf[3, sl] - buf[6, sl]).mean()))
+    print("M lane: before the waits - previous commit %.0f | waiting for B %.0f | then for the converters %.0f" %
+          ((buf[7, 21:141] - buf[4, sl]).mean(), (buf[2, sl] - buf[7, sl]).mean(), (buf[3, sl] - buf[2, sl]).mean()))
 
 
 if __name__ == "__main__":
