@@ -92,12 +92,9 @@ def trace():
         print("%-16s mean period %.0f" % (n, np.diff(buf[r, 20:140]).mean()))
     sl = slice(20, 140)
     print("means: landed - empty seen %.0f | arrived - landed %.0f | M full seen - arrived %.0f | commit - full seen %.0f | "
-          "next full seen - commit %.0f | last team warp arrived - first %.0f | M full seen - last arrive %.0f" %
-          ((buf[0, sl] - buf[5, sl]).mean(), (buf[1, sl] - buf[0, sl]).mean(),
-           (buf[3, sl] - buf[1, sl]).mean(), (buf[4, sl] - buf[3, sl]).mean(),
-           (buf[3, 21:141] - buf[4, sl]).mean(), (buf[6, sl] - buf[1, sl]).mean(), (buf[3, sl] - buf[6, sl]).mean()))
-    print("M lane: before the waits - previous commit %.0f | waiting for B %.0f | then for the converters %.0f" %
-          ((buf[7, 21:141] - buf[4, sl]).mean(), (buf[2, sl] - buf[7, sl]).mean(), (buf[3, sl] - buf[2, sl]).mean()))
+          "next full seen - commit %.0f" %
+          ((buf[0, sl] - buf[5, sl]).mean(), (buf[1, sl] - buf[0, sl]).mean(), (buf[3, sl] - buf[1, sl]).mean(),
+           (buf[4, sl] - buf[3, sl]).mean(), (buf[3, 21:141] - buf[4, sl]).mean()))
 
 
 if __name__ == "__main__":
