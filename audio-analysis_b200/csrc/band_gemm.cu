@@ -18,17 +18,25 @@
 // over the 900 accumulations of a whole chunk (hop 2400) that is a systematic -1.7e-5 relative shrink (measured,
 // profiles/r3_experiments.md).  So the accumulator is restarted every kBgSegKb k-blocks (18 accumulations) and the
 // segments are summed in FP32 registers with round-to-nearest by the epilogue warps, which own a whole 128-column row
-// each (176 registers through setmaxnreg, taken from the producer / MMA warps).
+// each (168 registers through setmaxnreg, taken from the producer / MMA warpgroups).
 //
-// One persistent CTA per SM, warp-specialised:
-//   warps 0-7   producers of A: 16-byte cp.async of the raw samples into the 64-byte-swizzled K-major stage three
-//               k-blocks ahead, then (own chunks only, no cross-thread hand-over) hi / lo split in place
-//   warp  8     one lane: bulk copy (cp.async.bulk, the TMA engine's linear mode) of the pre-swizzled B k-block
-//   warp  9     one lane: 12 tcgen05.mma (M 128, N 128, K 8; two row halves x three products x two k-steps) per
-//               k-block, tcgen05.commit to the stage's empty barrier / the accumulator's full barrier
-//   warps 12-19 epilogue: tcgen05.ld of every finished segment accumulator (256 x 128, double-buffered: all 512 TMEM
-//               columns), running sums in registers, P rows to global memory after the tile's last segment
-// band_frames_kernel then forms the frames (sum of two P rows, Hann taps, magnitude).
+// One persistent CTA per SM (640 threads), warp-specialised around four 48 KB stages [A hi | A lo | B hi | B lo] of one
+// 16-sample k-block each; every hand-over is an mbarrier.  The kernel is templated on how A arrives:
+//   TMA form (equally long recordings of a whole number of hops, back to back: the buffer IS a [chunks x hop] matrix)
+//     warp  8     one lane: per k-block ONE cp.async.bulk.tensor.2d box (256 chunk rows x 16 samples, 64-byte swizzle, rows
+//                 past the end zero-filled) into A hi, and the bulk copy (cp.async.bulk) of the pre-swizzled B k-block
+//     warps 0-7   converters, two teams alternating k-blocks: A lo from the landed samples (the raw sample stays as
+//                 the hi operand: the MMA ignores the low 13 mantissa bits), fence.proxy.async, arrive
+//   cp.async form (any batch whose recordings start on 16-byte boundaries, ragged lengths included)
+//     warps 0-7   producers: 16-byte cp.async of the raw samples through a per-tile row table, three k-blocks ahead,
+//                 then hi / lo split in place (own chunks only, no cross-thread hand-over)
+//     warp  8     one lane: bulk copy of the B k-block
+//   both forms
+//     warp  9     one lane: 6 tcgen05.mma per k-block (M = 128 columns of P, N = 256 chunk rows, K = 8: three products x
+//                 two k-steps), tcgen05.commit to the stage's empty barrier / the accumulator's full barrier
+//     warps 12-19 epilogue: tcgen05.ld of every finished segment accumulator (128 x 256, double-buffered: all 512 TMEM
+//                 columns), running sums in registers, P rows to global memory after the tile's last segment
+// band_frames_kernel / band_frames_uniform_kernel then form the frames (sum of two P rows, Hann taps, magnitude).
 #include <cuda.h>
 #include <cstdint>
 #include <cstring>
