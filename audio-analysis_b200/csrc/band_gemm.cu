@@ -25,8 +25,8 @@
 //   TMA form (equally long recordings of a whole number of hops, back to back: the buffer IS a [chunks x hop] matrix)
 //     warp  8     one lane: per k-block ONE cp.async.bulk.tensor.2d box (256 chunk rows x 16 samples, 64-byte swizzle, rows
 //                 past the end zero-filled) into A hi, and the bulk copy (cp.async.bulk) of the pre-swizzled B k-block
-//     warps 0-7   converters, two teams alternating k-blocks: A lo from the landed samples (the raw sample stays as
-//                 the hi operand: the MMA ignores the low 13 mantissa bits), fence.proxy.async, arrive
+//     warps 0-7   converters, 4 chunks of every k-block per thread: A lo from the landed samples (the raw sample stays
+//                 as the hi operand: the MMA ignores the low 13 mantissa bits), fence.proxy.async, arrive
 //   cp.async form (any batch whose recordings start on 16-byte boundaries, ragged lengths included)
 //     warps 0-7   producers: 16-byte cp.async of the raw samples through a per-tile row table, three k-blocks ahead,
 //                 then hi / lo split in place (own chunks only, no cross-thread hand-over)
@@ -197,7 +197,7 @@ band_gemm_kernel(const __grid_constant__ CUtensorMap a_map, const float* __restr
     if (tid == 0) {
         for (int s = 0; s < kBgStages; ++s) {
             mbar_init(&S.landed[s], 1);
-            mbar_init(&S.full[s], (kTma ? kBgProducerWarps / 2 : kBgProducerWarps) + 1);
+            mbar_init(&S.full[s], kBgProducerWarps + 1);
             mbar_init(&S.empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) { mbar_init(&S.acc_full[a], 1); mbar_init(&S.acc_empty[a], kBgEpiWarps); }
@@ -216,41 +216,36 @@ band_gemm_kernel(const __grid_constant__ CUtensorMap a_map, const float* __restr
     if (kTma && warp < kBgProducerWarps) {
         // ===== converters (TMA mode): the lo operand of the landed samples, lo = x - (x with the low 13 mantissa bits cleared).
         // The hi operand is the raw sample as it landed: the MMA reads the top 19 bits of an FP32 operand and ignores the
-        // rest (measured: rewriting the truncated value changes no bit of the result).  Team warp / 4 takes every other
-        // k-block, so a team has two k-block times for its wait -> LDS -> STS -> fence -> arrive chain.  Thread owns chunk
-        // c of the rows r0 + 32 i. =====
+        // rest (measured: rewriting the truncated value changes no bit of the result).  All eight warps work on every
+        // k-block (two teams alternating k-blocks, 8 chunks per thread, had the longer landed -> arrived chain and were
+        // 5 % slower). =====
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kBgRegsProd));
-        const int team = tid >> 7, t = tid & 127;
-        const int c = t & 3, r0 = t >> 2;
-        const int soff0 = sw64_offset(r0, c);                              // + 2048 i: (row >> 1) & 3 does not depend on i
+        const int c = tid & 3, r0 = tid >> 2;                              // all eight warps on every k-block: rows r0 + 64 i
+        const int soff0 = sw64_offset(r0, c);                              // + 4096 i: (row >> 1) & 3 does not depend on i
         long long n = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
             for (int kb = 0; kb < n_kb; ++kb, ++n) {
-                if ((int)(n & 1) != team) continue;
                 const int st = (int)(n & (kBgStages - 1));
                 mbar_wait_warp(&S.landed[st], (unsigned)((n / kBgStages) & 1), lane);
-                if (t == 0) BG_TRACE(0, (int)n);
+                if (tid == 0) BG_TRACE(0, (int)n);
                 const unsigned char* a_hi = stages + (size_t)st * kBgStageBytes + soff0;
                 unsigned char* a_lo = stages + (size_t)st * kBgStageBytes + kBgABytes + soff0;
+                float4 v[4];
 #pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    float4 v[4];
+                for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const float4*>(a_hi + 4096 * i);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) v[i] = *reinterpret_cast<const float4*>(a_hi + 2048 * (4 * half + i));
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float4 l;
-                        l.x = v[i].x - __uint_as_float(__float_as_uint(v[i].x) & 0xffffe000u);
-                        l.y = v[i].y - __uint_as_float(__float_as_uint(v[i].y) & 0xffffe000u);
-                        l.z = v[i].z - __uint_as_float(__float_as_uint(v[i].z) & 0xffffe000u);
-                        l.w = v[i].w - __uint_as_float(__float_as_uint(v[i].w) & 0xffffe000u);
-                        *reinterpret_cast<float4*>(a_lo + 2048 * (4 * half + i)) = l;
-                    }
+                for (int i = 0; i < 4; ++i) {
+                    float4 l;
+                    l.x = v[i].x - __uint_as_float(__float_as_uint(v[i].x) & 0xffffe000u);
+                    l.y = v[i].y - __uint_as_float(__float_as_uint(v[i].y) & 0xffffe000u);
+                    l.z = v[i].z - __uint_as_float(__float_as_uint(v[i].z) & 0xffffe000u);
+                    l.w = v[i].w - __uint_as_float(__float_as_uint(v[i].w) & 0xffffe000u);
+                    *reinterpret_cast<float4*>(a_lo + 4096 * i) = l;
                 }
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&S.full[st]);
-                if (t == 0) BG_TRACE(1, (int)n);
+                if (tid == 0) BG_TRACE(1, (int)n);
             }
     } else if (warp < kBgProducerWarps) {
         // ===== A producers (cp.async mode): thread owns chunk c of rows r0 + 64 i =====
