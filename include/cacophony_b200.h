@@ -202,7 +202,13 @@ int32_t cac_spec_rows(const cac_spec_plan* plan);
 /* Spectra of n_items recordings stored in d_pcm at h_item_offset[i] (h_item_samples[i] samples).
  * Frames are numbered globally, recording after recording.  Output: mel -> per recording
  * [n_mels][frames_i] (recordings back to back); raw -> see bin_major.  d_max (may be NULL)
- * receives the largest |X|**power produced (signal_noise's a_max, src/identify_tracks.py:656). */
+ * receives the largest |X|**power produced (signal_noise's a_max, src/identify_tracks.py:656).
+ * Raw-band plans with hop_length = n_fft / 2, hop_length a multiple of 16 and at most 62 bins (identify_morepork's
+ * spectrogram, src/identify_morepork.py:19-27) run as a tensor-core GEMM (tcgen05, csrc/band_gemm.cu) when every recording
+ * starts on a 16-byte boundary - through one TMA tensor map when the recordings are equally long, a whole number of hops
+ * and back to back; max error 1-3e-6 of the spectrum maximum instead of 1e-7 (BASELINE's bar for the path: 1e-2 dB).
+ * The environment variable CAC_BAND_GEMM=0 keeps the FFT kernels for such plans.  The plan grows a scratch buffer of
+ * 512 bytes per frame for it on the first call (cudaMalloc; like the item table this entry point stages). */
 int cac_spec_run(cac_spec_plan* plan, const float* d_pcm, const int64_t* h_item_offset, const int64_t* h_item_samples,
                  int64_t n_items, float* d_out, float* d_max, void* stream);
 /* d_data[i] /= *d_max  (spectogram / a_max, src/identify_tracks.py:657) */
