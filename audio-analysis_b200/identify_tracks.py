@@ -332,7 +332,7 @@ def signal_noise(frames, sr, hop_length=281, signal_cls=None):
 def classify_prep_batch(recordings, sr, segment_length=3, segment_stride=1.5, hop_length=281, mean_sub=False,
                         mel_break=1000, htk=True, n_mels=160, fmin=50, fmax=11000, channels=1, power=2, db_scale=False,
                         normalize=True, n_fft=4096, pad_short_tracks=False, max_components=1024, want_samples=True,
-                        chunk=64):
+                        chunk=24):
     """Everything classify does to a recording before its model runs (src/identify_tracks.py:416-440, 502-524) for a
     batch of decoded recordings.  The batch goes through in chunks of `chunk` recordings, and per chunk:
       1. get_end -> signal_noise(frames[: int(sr * length)]) chained on the device (the trimmed lengths are computed on

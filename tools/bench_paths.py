@@ -162,7 +162,7 @@ def path_pipeline(n_rec=256, cpu=True):
            "phases_ms_per_recording": {"get_end_batch": ge_ms / n_rec, "signal_noise_batch": sn_ms / n_rec,
                                        "host_merge_and_load_samples": max(0.0, total_ms - ge_ms - sn_ms) / n_rec},
            "dominant_kernel": "sn_stft_kernel" if sn_ms >= ge_ms else "spec4800_kernel<75>", "dtype": "f32",
-           "synchronisations": "one per 64-recording chunk; the host merge of chunk i overlaps the kernels of chunk i + 1"}
+           "synchronisations": "one per 24-recording chunk; the host merge of chunk i overlaps the kernels of chunk i + 1"}
     del res
     if cpu:
         from oracle import oracle_np as O
