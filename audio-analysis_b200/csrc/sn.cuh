@@ -47,7 +47,7 @@ cudaError_t launch_sn_prep(const long long* d_item_off, const long long* d_item_
 cudaError_t launch_sn_stft(const float* pcm, const SnWave& w, int hop, int frames_per_stage, cudaStream_t st);
 // sn_rows.cu
 cudaError_t launch_sn_col_thresholds(const SnWave& w, int max_cols, cudaStream_t st);
-cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, cudaStream_t st);
+cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, bool aligned_rows, cudaStream_t st);
 constexpr int kSnMaxColsFast = 512 * 48;                     // longest row the register-resident select covers
 // track_bits.cu (batched over the wave)
 cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp_plane, int dst_plane, int max_wpr, int kh,

@@ -175,7 +175,7 @@ extern "C" int cac_sn_run(cac_sn_plan* plan, const float* d_pcm, const int64_t* 
                                 (long long)max_item_samples, const_cast<SnItem*>(w.items), w.amax, st));
         CUDA_TRY(launch_sn_stft(d_pcm, w, plan->hop, plan->fps, st));
         CUDA_TRY(launch_sn_col_thresholds(w, (int)max_cols, st));
-        CUDA_TRY(launch_sn_rowmed_mask(w, (int)max_cols, st));
+        CUDA_TRY(launch_sn_rowmed_mask(w, (int)max_cols, true, st));
         int rc = mask_chain(w, L, plan->dilate_h, plan->dilate_w, plan->erode_h, nullptr, 0, st);
         if (rc) return rc;
     }
@@ -232,6 +232,7 @@ extern "C" int cac_signal_components_run(const float* d_spec, int32_t rows, int6
     CUDA_TRY(launch_transpose(d_spec, scratch, rows, cols, st));
     CUDA_TRY(launch_row_median(scratch, w.colmed, cols, rows, st));
     CUDA_TRY(launch_sn_col_thresholds(w, (int)cols, st));
-    CUDA_TRY(launch_sn_rowmed_mask(w, (int)cols, st));
+    const bool aligned_rows = cols % 4 == 0 && ((uintptr_t)d_spec & 15) == 0;     // pitch = cols here
+    CUDA_TRY(launch_sn_rowmed_mask(w, (int)cols, aligned_rows, st));
     return mask_chain(w, L, dilate_h, dilate_w, erode_h, d_stage_masks, 0, st);
 }

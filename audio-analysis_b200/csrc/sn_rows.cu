@@ -151,6 +151,239 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_kernel(const SnWave w
     }
 }
 
+// ---- the same row step for matrices with 16-byte aligned rows (every matrix the fused chain produces) ------------------
+// ncu's source view of the kernel above (profiles/r3j_sn_rowmed_lines.txt): 2,100 instructions per thread and row, the
+// issue slots 64 % busy - the kernel is bound by its INSTRUCTION COUNT, not by the histogram atomics or by HBM.  This
+// version does the same select and mask in about a third of the instructions:
+//   * thread t holds the columns 4 t + 4 NT v + {0..3}: one 16-byte load per four keys, one threshold load per four
+//     columns, the mask word of 32 columns assembled from eight lanes' nibbles by three shuffles;
+//   * ONE histogram pass over all keys (12 bits below the common prefix of the row's extremes, no per-key prefix or
+//     bounds test: key slots beyond the row hold 0x80000000, which lands in bin 0 and is subtracted there);
+//   * the handful of keys of the selected bin (typically < 20 of 10,250) are compacted into shared memory and the
+//     order statistic is found among them by counting - instead of two more passes over all 10,250 keys;
+//   * the second middle value of an even row comes from the same candidates, or - when the first one is the largest of
+//     its bin - from one min-pass over the keys above the bin; the separate count / min pass is gone.
+// A bin with more candidates than threads (heavy ties) continues with the histogram passes of the kernel above.
+constexpr unsigned kNoKey = 0x80000000u;      // -0.0f: above every magnitude as unsigned, below as signed, never > t
+
+struct RowSelV {
+    unsigned hist[kSelCtaBins];
+    unsigned tot[32];
+    unsigned out[4];                          // bin, rank inside the bin, keys in the bin
+    unsigned mn;
+    int mx;
+    unsigned ncand, v1, v2, cnt_le, min_gt;
+    unsigned cand[1024];
+};
+
+// bin of `hist` that holds rank k, the rank inside it and the bin's count -> out[0..2]; n_pad keys are taken off bin 0
+// (slots beyond the row).  All NT threads call; ends with a barrier.
+template <int NT>
+__device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k, unsigned n_pad, unsigned* s_tot, unsigned* out) {
+    constexpr int BPT = kSelCtaBins / NT, NW = NT / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint4* h4 = reinterpret_cast<const uint4*>(hist) + tid * (BPT / 4);
+    unsigned bins[BPT];
+    unsigned sum = 0;
+#pragma unroll
+    for (int i = 0; i < BPT / 4; ++i) {
+        const uint4 q = h4[i];
+        bins[4 * i] = q.x; bins[4 * i + 1] = q.y; bins[4 * i + 2] = q.z; bins[4 * i + 3] = q.w;
+    }
+    if (tid == 0) bins[0] -= n_pad;
+#pragma unroll
+    for (int i = 0; i < BPT; ++i) sum += bins[i];
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+    }
+    if (lane == 31) s_tot[warp] = inc;
+    __syncthreads();
+    unsigned wt = lane < NW ? s_tot[lane] : 0u;             // exclusive scan of the warp totals, redone by every warp
+    unsigned winc = wt;
+#pragma unroll
+    for (int o = 1; o < NW; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += up;
+    }
+    const unsigned base = __shfl_sync(0xffffffffu, winc - wt, warp);
+    const unsigned exc = base + inc - sum;
+    if (k >= exc && k < exc + sum) {                        // exactly one thread
+        unsigned kk = k - exc, b = 0, cnt = bins[0];
+#pragma unroll
+        for (int i = 0; i < BPT - 1; ++i)
+            if (b == (unsigned)i && kk >= bins[i]) { kk -= bins[i]; b = i + 1; cnt = bins[i + 1]; }
+        out[0] = (unsigned)(tid * BPT) + b;
+        out[1] = kk;
+        out[2] = cnt;
+    }
+    __syncthreads();
+}
+
+template <int NT, int V, int MINB>
+__global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWave w) {
+    static_assert(NT <= 1024 && kSelCtaBins % (4 * NT) == 0, "threads per CTA");
+    __shared__ __align__(16) RowSelV s;
+    const int item = blockIdx.y, row = blockIdx.x;
+    const SnItem im = w.items[item];
+    const int cols = im.cols;
+    if (cols < 1 || cols > 4 * NT * V) return;              // served by a wider instantiation (launch_sn_rowmed_mask)
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned* rowp = reinterpret_cast<const unsigned*>(w.spec + (size_t)item * w.spec_stride) + (size_t)row * im.pitch;
+    const int c0 = 4 * tid;
+    unsigned key[4 * V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+        const int c = c0 + 4 * NT * v;
+        uint4 q = make_uint4(kNoKey, kNoKey, kNoKey, kNoKey);
+        if (c < cols) q = __ldg(reinterpret_cast<const uint4*>(rowp + c));      // the pitch is a multiple of 32 floats
+        key[4 * v] = q.x; key[4 * v + 1] = q.y; key[4 * v + 2] = q.z; key[4 * v + 3] = q.w;
+    }
+    if (tid == 0) { s.mn = 0xffffffffu; s.mx = 0; s.ncand = 0u; s.v1 = 0u; s.v2 = 0u; s.cnt_le = 0u; s.min_gt = 0xffffffffu; }
+    {                                                       // the vector that straddles the end of the row
+        const int cb = cols & ~3, vb = cb / (4 * NT);
+        if ((cols & 3) && c0 + 4 * NT * vb == cb) {
+#pragma unroll
+            for (int v = 0; v < V; ++v)
+                if (v == vb) {
+#pragma unroll
+                    for (int j = 1; j < 4; ++j)
+                        if (j >= (cols & 3)) key[4 * v + j] = kNoKey;
+                }
+        }
+    }
+    unsigned mn = 0xffffffffu;
+    int mx = 0;
+#pragma unroll
+    for (int i = 0; i < 4 * V; ++i) { mn = min(mn, key[i]); mx = max(mx, (int)key[i]); }
+    __syncthreads();
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0) { atomicMin(&s.mn, mn); atomicMax(&s.mx, mx); }
+    uint4* h4 = reinterpret_cast<uint4*>(s.hist);
+#pragma unroll
+    for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    const unsigned lo = s.mn, hi = (unsigned)s.mx;
+    const unsigned k0 = (unsigned)((cols - 1) / 2);
+    const bool even = (cols & 1) == 0;
+    unsigned v1 = hi, v2 = hi;
+    if (lo != hi) {                                         // uniform for the CTA
+        int remaining = 32 - __clz(lo ^ hi);                // bits [0, remaining) vary; <= 31
+        unsigned prefix = (hi >> remaining) << remaining;
+        const int wd = min(kSelCtaBits, remaining), shift = remaining - wd;
+        const unsigned dmask = (1u << wd) - 1u;
+#pragma unroll
+        for (int v = 0; v < V; ++v)
+            if (c0 + 4 * NT * v < cols) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) atomicAdd(s.hist + ((key[4 * v + j] >> shift) & dmask), 1u);
+            }
+        __syncthreads();
+        sel_scan_cta_v<NT>(s.hist, k0, (unsigned)((4 - (cols & 3)) & 3), s.tot, s.out);
+        const unsigned b = s.out[0], kin = s.out[1], hb = s.out[2];
+        prefix |= b << shift;
+        bool second_above = even && kin + 1u >= hb;         // the next order statistic lies above this bin
+        if (shift == 0) {
+            v1 = v2 = prefix;
+        } else if (hb <= (unsigned)NT) {
+            // the bin's keys -> shared memory; rank k of them = the largest key with at most k keys below it
+            const unsigned fmask = (dmask << shift) | 0x80000000u, fval = b << shift;
+#pragma unroll
+            for (int i = 0; i < 4 * V; ++i)
+                if ((key[i] & fmask) == fval) s.cand[atomicAdd(&s.ncand, 1u)] = key[i];
+            __syncthreads();
+            if ((unsigned)(tid & ~31) < hb) {               // warps that own a candidate
+                const unsigned my = (unsigned)tid < hb ? s.cand[tid] : 0u;
+                unsigned lt = 0u;
+#pragma unroll 4
+                for (unsigned i = 0; i < hb; ++i) lt += (s.cand[i] - my) >> 31;       // keys < 2^31: x < my <=> borrow
+                const bool mine = (unsigned)tid < hb;
+                const unsigned a1 = __reduce_max_sync(0xffffffffu, mine && lt <= kin ? my : 0u);
+                const unsigned a2 = __reduce_max_sync(0xffffffffu, mine && lt <= kin + 1u ? my : 0u);
+                if (lane == 0) { atomicMax(&s.v1, a1); atomicMax(&s.v2, a2); }
+            }
+            __syncthreads();
+            v1 = s.v1;
+            v2 = s.v2;
+        } else {
+            // heavy ties: more keys in the bin than threads - the remaining digits by histogram passes
+            unsigned k = kin;
+            remaining = shift;
+#pragma unroll 1
+            while (remaining > 0) {
+                const int wd2 = min(kSelCtaBits, remaining), shift2 = remaining - wd2;
+                const unsigned dmask2 = (1u << wd2) - 1u;
+                const unsigned above = (0xffffffffu << remaining) | 0x80000000u;       // bits fixed so far + the pad bit
+#pragma unroll
+                for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
+                __syncthreads();
+#pragma unroll
+                for (int i = 0; i < 4 * V; ++i)
+                    if (((key[i] ^ prefix) & above) == 0u) atomicAdd(s.hist + ((key[i] >> shift2) & dmask2), 1u);
+                __syncthreads();
+                sel_scan_cta_v<NT>(s.hist, k, 0u, s.tot, s.out);
+                prefix |= s.out[0] << shift2;
+                k = s.out[1];
+                remaining = shift2;
+                __syncthreads();
+            }
+            v1 = prefix;
+            if (even) {                                     // as the kernel above: count <= v1, smallest key above it
+                unsigned cnt = 0u, gt = 0xffffffffu;
+#pragma unroll
+                for (int i = 0; i < 4 * V; ++i) {
+                    if (key[i] <= v1) ++cnt; else gt = min(gt, key[i]);
+                }
+                cnt = __reduce_add_sync(0xffffffffu, cnt);
+                gt = __reduce_min_sync(0xffffffffu, gt);
+                if (lane == 0) { atomicAdd(&s.cnt_le, cnt); atomicMin(&s.min_gt, gt); }
+                __syncthreads();
+                v2 = s.cnt_le >= k0 + 2u ? v1 : s.min_gt;
+            }
+            second_above = false;
+        }
+        if (second_above) {                                 // smallest key above the bin (the pad value is above all)
+            const unsigned lim = ((prefix >> shift) + 1u) << shift;
+            unsigned gt = 0xffffffffu;
+#pragma unroll
+            for (int i = 0; i < 4 * V; ++i)
+                if (key[i] >= lim) gt = min(gt, key[i]);
+            gt = __reduce_min_sync(0xffffffffu, gt);
+            if (lane == 0) atomicMin(&s.min_gt, gt);
+            __syncthreads();
+            v2 = s.min_gt;
+        }
+    }
+    const float a = __uint_as_float(w.amax[item]);
+    float med = __fdiv_rn(__uint_as_float(v1), a);
+    if (even) med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);   // np.mean of the two middle values
+    const float tr = unscaled_threshold(__fmul_rn(3.0f, med), a);
+    const float* thr = w.colthr + (size_t)item * w.col_stride;
+    unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
+    const int sh = 4 * (lane & 7);
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+        const int c = c0 + 4 * NT * v;
+        if (4 * NT * v + 128 * (tid >> 5) >= 32 * im.wpr) break;          // warp-uniform: none of its words exists
+        unsigned nib = 0u;
+        if (c < cols) {                                     // the stride of the thresholds is a multiple of 32 floats
+            const float4 t4 = __ldg(reinterpret_cast<const float4*>(thr + c));
+            const float x0 = __uint_as_float(key[4 * v]), x1 = __uint_as_float(key[4 * v + 1]);
+            const float x2 = __uint_as_float(key[4 * v + 2]), x3 = __uint_as_float(key[4 * v + 3]);
+            nib = (x0 > t4.x && x0 > tr ? 1u : 0u) | (x1 > t4.y && x1 > tr ? 2u : 0u) | (x2 > t4.z && x2 > tr ? 4u : 0u) |
+                  (x3 > t4.w && x3 > tr ? 8u : 0u);
+        }
+        unsigned word = nib << sh;
+        word |= __shfl_xor_sync(0xffffffffu, word, 1);
+        word |= __shfl_xor_sync(0xffffffffu, word, 2);
+        word |= __shfl_xor_sync(0xffffffffu, word, 4);
+        if ((lane & 7) == 0 && (c >> 5) < im.wpr) bits[c >> 5] = word;
+    }
+}
+
 // Rows longer than the register-resident variants cover (recordings of more than ~4 minutes at hop 281):
 // the same select with the row re-read from global memory (L2) in every pass.
 __global__ void __launch_bounds__(256) sn_rowmed_mask_long_kernel(const SnWave w) {
@@ -229,21 +462,28 @@ cudaError_t launch_sn_col_thresholds(const SnWave& w, int max_cols, cudaStream_t
 }
 
 // max_cols = upper bound of the wave's row length: picks the narrowest register-resident variant that covers it
-// (recordings of a wave that are much shorter just predicate the tail off)
-cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, cudaStream_t st) {
+// (recordings of a wave that are much shorter just predicate the tail off).  aligned_rows: every row of every matrix
+// starts on a 16-byte boundary and is padded to whole 16-byte groups (the fused chain's own matrices: pitch = a
+// multiple of 32 floats) -> the vector kernel; a caller's matrix of any pitch -> the scalar one.
+// CAC_SN_ROWS_VARIANT=0 forces the scalar kernel (A/B runs).
+cudaError_t launch_sn_rowmed_mask(const SnWave& w, int max_cols, bool aligned_rows, cudaStream_t st) {
     dim3 grid((unsigned)w.rows, (unsigned)w.n_items);
+    static const int variant = getenv("CAC_SN_ROWS_VARIANT") ? atoi(getenv("CAC_SN_ROWS_VARIANT")) : 1;
+    if (aligned_rows && variant != 0) {
+        if (max_cols <= 256 * 8) sn_rowmed_mask_vec_kernel<256, 2, 4><<<grid, 256, 0, st>>>(w);
+        else if (max_cols <= 256 * 16) sn_rowmed_mask_vec_kernel<256, 4, 4><<<grid, 256, 0, st>>>(w);
+        else if (max_cols <= 256 * 32) sn_rowmed_mask_vec_kernel<256, 8, 4><<<grid, 256, 0, st>>>(w);
+        else if (max_cols <= 512 * 24) sn_rowmed_mask_vec_kernel<512, 6, 2><<<grid, 512, 0, st>>>(w);   // one minute: 10,250
+        else {
+            sn_rowmed_mask_vec_kernel<512, 12, 1><<<grid, 512, 0, st>>>(w);      // rows up to 24,576 columns
+            if (max_cols > kSnMaxColsFast) sn_rowmed_mask_long_kernel<<<grid, 256, 0, st>>>(w);   // the longer ones
+        }
+        return cudaGetLastError();
+    }
     if (max_cols <= 256 * 8) sn_rowmed_mask_kernel<256, 8><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 16) sn_rowmed_mask_kernel<256, 16><<<grid, 256, 0, st>>>(w);
     else if (max_cols <= 256 * 32) sn_rowmed_mask_kernel<256, 32><<<grid, 256, 0, st>>>(w);
-    else if (max_cols <= 256 * 44) {                      // one-minute recordings: 10,250 columns
-        // 512 threads x 22 keys at two CTAs per SM: measured fastest of {256 x 44, 512 x 22, 1024 x 11} (0.38 / 0.28 /
-        // 0.30-0.34 ms per recording for the whole chain, profiles/r3_experiments.md); CAC_SN_ROWS_VARIANT picks another
-        static const int variant = getenv("CAC_SN_ROWS_VARIANT") ? atoi(getenv("CAC_SN_ROWS_VARIANT")) : 1;
-        if (variant == 0) sn_rowmed_mask_kernel<256, 44><<<grid, 256, 0, st>>>(w);
-        else if (variant == 2) sn_rowmed_mask_kernel<1024, 11, 1><<<grid, 1024, 0, st>>>(w);
-        else if (variant == 3) sn_rowmed_mask_kernel<1024, 11, 2><<<grid, 1024, 0, st>>>(w);
-        else sn_rowmed_mask_kernel<512, 22, 2><<<grid, 512, 0, st>>>(w);
-    }
+    else if (max_cols <= 256 * 44) sn_rowmed_mask_kernel<512, 22, 2><<<grid, 512, 0, st>>>(w);
     else {
         sn_rowmed_mask_kernel<512, 48><<<grid, 512, 0, st>>>(w);         // rows up to 24,576 columns
         if (max_cols > kSnMaxColsFast) sn_rowmed_mask_long_kernel<<<grid, 256, 0, st>>>(w);   // the longer ones

@@ -46,6 +46,41 @@ def test_row_medians_exact(engine):
         assert np.array_equal(masks[0].cpu().numpy(), ref.astype(np.uint8)), shape
 
 
+@pytest.mark.parametrize("shape", [(9, 10252), (3, 4096), (3, 8192), (2, 20000), (2, 24576), (5, 1000), (4, 4), (3, 12288)])
+def test_row_medians_exact_on_16_byte_aligned_rows(engine, shape):
+    """Matrices whose rows are whole 16-byte groups take sn_rowmed_mask_vec_kernel (one histogram pass, candidates ranked
+    in shared memory) - the kernel the fused chain uses.  Rows built to reach each of its branches: plain noise, a wide
+    dynamic range, ties by the thousand around the median (more candidates than threads: histogram passes), a constant
+    row, a row of zeros, keys that differ only in their low 12 bits (no second digit), two-valued rows whose middle
+    values sit in different bins, and a row with a handful of duplicates of the median."""
+    import torch
+    rng = np.random.default_rng(shape[1])
+    rows, cols = shape
+    x = np.abs(rng.standard_normal(shape)).astype(np.float32)
+    x[0, : cols // 2] = 0.25
+    if rows > 1:
+        x[1] = np.exp(5.0 * rng.standard_normal(cols)).astype(np.float32)
+    if rows > 2:
+        x[2] = 0.5
+    if rows > 3:
+        x[3] = 0.0
+    if rows > 4:
+        x[4] = (np.uint32(0x3f000000) + rng.integers(0, 4096, cols).astype(np.uint32)).view(np.float32)
+    if rows > 5:
+        x[5] = np.where(np.arange(cols) % 2 == 0, np.float32(0.001), np.float32(7.0))
+    if rows > 6:
+        x[6, :5] = np.sort(x[6])[cols // 2]
+    if rows > 7:
+        x[7] = np.round(x[7] * 8) / 8                                  # ~30 distinct values
+    t = torch.from_numpy(x).cuda()
+    assert t.data_ptr() % 16 == 0
+    stats, masks = engine.signal_components(t, 1, 1, 1, want_masks=True)
+    ref = (x > 3 * np.median(x, axis=0)[None, :]) & (x > 3 * np.median(x, axis=1)[:, None])
+    got = masks[0].cpu().numpy()
+    bad = np.argwhere(got != ref.astype(np.uint8))
+    assert len(bad) == 0, (shape, bad[:5])
+
+
 @pytest.mark.parametrize("name,seed,seconds", CASES)
 def test_signal_noise_equals_reference_fixture(engine, golden, name, seed, seconds):
     from audio_analysis_b200 import identify_tracks as T
