@@ -154,32 +154,37 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_kernel(const SnWave w
 // ---- the same row step for matrices with 16-byte aligned rows (every matrix the fused chain produces) ------------------
 // ncu's source view of the kernel above (profiles/r3j_sn_rowmed_lines.txt): 2,100 instructions per thread and row, the
 // issue slots 64 % busy - the kernel is bound by its INSTRUCTION COUNT, not by the histogram atomics or by HBM.  This
-// version does the same select and mask in about a third of the instructions:
+// version does the same select and mask in well under half the instructions:
 //   * thread t holds the columns 4 t + 4 NT v + {0..3}: one 16-byte load per four keys, one threshold load per four
 //     columns, the mask word of 32 columns assembled from eight lanes' nibbles by three shuffles;
-//   * ONE histogram pass over all keys (12 bits below the common prefix of the row's extremes, no per-key prefix or
-//     bounds test: key slots beyond the row hold 0x80000000, which lands in bin 0 and is subtracted there);
-//   * the handful of keys of the selected bin (typically < 20 of 10,250) are compacted into shared memory and the
-//     order statistic is found among them by counting - instead of two more passes over all 10,250 keys;
+//   * a BRACKET [L, L + span] for the median from 32 keys spread over the row (sorted by every warp with shuffles; the
+//     bracket is the sample's ranks 6 and 25, which misses the median of one row in about a thousand);
+//   * ONE pass over the keys: keys below L are counted, keys inside the bracket go to bin (key - L) >> shift of a
+//     4,096-bin histogram that spans exactly the bracket - so the bin that holds the median has a few keys, where the
+//     top 12 varying bits of the whole row (the kernel above) leave hundreds of keys for two more passes;
+//   * those few keys are compacted into shared memory and the order statistic is found among them by counting;
 //   * the second middle value of an even row comes from the same candidates, or - when the first one is the largest of
-//     its bin - from one min-pass over the keys above the bin; the separate count / min pass is gone.
-// A bin with more candidates than threads (heavy ties) continues with the histogram passes of the kernel above.
+//     its bin - from one min-pass over the keys above the bin.
+// The bracket only steers: the counts are exact, and when the rank turns out to lie outside it (or the row is too
+// short to sample) the pass is redone with the row's minimum and maximum as the bracket; a bin with more keys than
+// threads (heavy ties) becomes the next, narrower bracket.
 constexpr unsigned kNoKey = 0x80000000u;      // -0.0f: above every magnitude as unsigned, below as signed, never > t
 
 struct RowSelV {
     unsigned hist[kSelCtaBins];
     unsigned tot[32];
-    unsigned out[4];                          // bin, rank inside the bin, keys in the bin
+    unsigned out[4];                          // bin, rank inside the bin, keys in the bin (0: rank not in the histogram)
     unsigned mn;
     int mx;
-    unsigned ncand, v1, v2, cnt_le, min_gt;
+    unsigned below, ncand, v1, v2, min_gt;
+    unsigned sample[32];
     unsigned cand[1024];
 };
 
-// bin of `hist` that holds rank k, the rank inside it and the bin's count -> out[0..2]; n_pad keys are taken off bin 0
-// (slots beyond the row).  All NT threads call; ends with a barrier.
+// bin of `hist` that holds rank k, the rank inside it and the bin's count -> out[0..2] (untouched when k is not below
+// the histogram's total).  All NT threads call; ends with a barrier.
 template <int NT>
-__device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k, unsigned n_pad, unsigned* s_tot, unsigned* out) {
+__device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k, unsigned* s_tot, unsigned* out) {
     constexpr int BPT = kSelCtaBins / NT, NW = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint4* h4 = reinterpret_cast<const uint4*>(hist) + tid * (BPT / 4);
@@ -189,10 +194,8 @@ __device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k,
     for (int i = 0; i < BPT / 4; ++i) {
         const uint4 q = h4[i];
         bins[4 * i] = q.x; bins[4 * i + 1] = q.y; bins[4 * i + 2] = q.z; bins[4 * i + 3] = q.w;
+        sum += q.x + q.y + q.z + q.w;
     }
-    if (tid == 0) bins[0] -= n_pad;
-#pragma unroll
-    for (int i = 0; i < BPT; ++i) sum += bins[i];
     unsigned inc = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -201,7 +204,7 @@ __device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k,
     }
     if (lane == 31) s_tot[warp] = inc;
     __syncthreads();
-    unsigned wt = lane < NW ? s_tot[lane] : 0u;             // exclusive scan of the warp totals, redone by every warp
+    const unsigned wt = lane < NW ? s_tot[lane] : 0u;       // exclusive scan of the warp totals, redone by every warp
     unsigned winc = wt;
 #pragma unroll
     for (int o = 1; o < NW; o <<= 1) {
@@ -210,7 +213,7 @@ __device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k,
     }
     const unsigned base = __shfl_sync(0xffffffffu, winc - wt, warp);
     const unsigned exc = base + inc - sum;
-    if (k >= exc && k < exc + sum) {                        // exactly one thread
+    if (k >= exc && k < exc + sum) {                        // at most one thread
         unsigned kk = k - exc, b = 0, cnt = bins[0];
 #pragma unroll
         for (int i = 0; i < BPT - 1; ++i)
@@ -222,9 +225,23 @@ __device__ __forceinline__ void sel_scan_cta_v(const unsigned* hist, unsigned k,
     __syncthreads();
 }
 
+// ascending bitonic sort of one value per lane
+__device__ __forceinline__ unsigned warp_sort32(unsigned x, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const unsigned y = __shfl_xor_sync(0xffffffffu, x, j);
+            const bool keep_min = ((lane & j) == 0) == ((lane & k) == 0);
+            x = keep_min ? min(x, y) : max(x, y);
+        }
+    }
+    return x;
+}
+
 template <int NT, int V, int MINB>
 __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWave w) {
-    static_assert(NT <= 1024 && kSelCtaBins % (4 * NT) == 0, "threads per CTA");
+    static_assert(NT <= 1024 && NT % 32 == 0 && kSelCtaBins % (4 * NT) == 0, "threads per CTA");
     __shared__ __align__(16) RowSelV s;
     const int item = blockIdx.y, row = blockIdx.x;
     const SnItem im = w.items[item];
@@ -241,7 +258,12 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
         if (c < cols) q = __ldg(reinterpret_cast<const uint4*>(rowp + c));      // the pitch is a multiple of 32 floats
         key[4 * v] = q.x; key[4 * v + 1] = q.y; key[4 * v + 2] = q.z; key[4 * v + 3] = q.w;
     }
-    if (tid == 0) { s.mn = 0xffffffffu; s.mx = 0; s.ncand = 0u; s.v1 = 0u; s.v2 = 0u; s.cnt_le = 0u; s.min_gt = 0xffffffffu; }
+    if (tid == 0) {
+        s.mn = 0xffffffffu; s.mx = 0; s.below = 0u; s.ncand = 0u; s.v1 = 0u; s.v2 = 0u; s.min_gt = 0xffffffffu; s.out[2] = 0u;
+    }
+    uint4* h4 = reinterpret_cast<uint4*>(s.hist);
+#pragma unroll
+    for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
     {                                                       // the vector that straddles the end of the row
         const int cb = cols & ~3, vb = cb / (4 * NT);
         if ((cols & 3) && c0 + 4 * NT * vb == cb) {
@@ -254,53 +276,85 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
                 }
         }
     }
-    unsigned mn = 0xffffffffu;
-    int mx = 0;
+    const int nv = cols / (4 * NT);                         // vector slots that are inside the row for every thread
+    bool have = nv >= 1;                                    // uniform
+    if (have && tid % (NT / 32) == 0) {                     // sample i: column 4 tid + 4 NT (i mod nv)
+        const int i = tid / (NT / 32), vs = i % nv;
+        unsigned sv = key[0];
 #pragma unroll
-    for (int i = 0; i < 4 * V; ++i) { mn = min(mn, key[i]); mx = max(mx, (int)key[i]); }
+        for (int v = 1; v < V; ++v)
+            if (v == vs) sv = key[4 * v];
+        s.sample[i] = sv;
+    }
     __syncthreads();
-    mn = __reduce_min_sync(0xffffffffu, mn);
-    mx = __reduce_max_sync(0xffffffffu, mx);
-    if (lane == 0) { atomicMin(&s.mn, mn); atomicMax(&s.mx, mx); }
-    uint4* h4 = reinterpret_cast<uint4*>(s.hist);
-#pragma unroll
-    for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
-    __syncthreads();
-    const unsigned lo = s.mn, hi = (unsigned)s.mx;
+    unsigned L = 0u, span = 0u;
+    if (have) {
+        const unsigned x = warp_sort32(s.sample[lane], lane);
+        L = __shfl_sync(0xffffffffu, x, 6);
+        span = __shfl_sync(0xffffffffu, x, 25) - L;
+    }
     const unsigned k0 = (unsigned)((cols - 1) / 2);
     const bool even = (cols & 1) == 0;
-    unsigned v1 = hi, v2 = hi;
-    if (lo != hi) {                                         // uniform for the CTA
-        int remaining = 32 - __clz(lo ^ hi);                // bits [0, remaining) vary; <= 31
-        unsigned prefix = (hi >> remaining) << remaining;
-        const int wd = min(kSelCtaBits, remaining), shift = remaining - wd;
-        const unsigned dmask = (1u << wd) - 1u;
+    unsigned v1 = 0u, v2 = 0u;
+#pragma unroll 1
+    for (int attempt = 0;; ++attempt) {                     // one trip for all but a handful of rows
+        if (attempt > 0) {
+            __syncthreads();
+            if (tid == 0) { s.below = 0u; s.ncand = 0u; s.v1 = 0u; s.v2 = 0u; s.out[2] = 0u; }
 #pragma unroll
-        for (int v = 0; v < V; ++v)
-            if (c0 + 4 * NT * v < cols) {
+            for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+        }
+        if (!have) {                                        // bracket = the row's extremes
+            unsigned mn = 0xffffffffu;
+            int mx = 0;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) atomicAdd(s.hist + ((key[4 * v + j] >> shift) & dmask), 1u);
-            }
+            for (int i = 0; i < 4 * V; ++i) { mn = min(mn, key[i]); mx = max(mx, (int)key[i]); }
+            mn = __reduce_min_sync(0xffffffffu, mn);
+            mx = __reduce_max_sync(0xffffffffu, mx);
+            if (lane == 0) { atomicMin(&s.mn, mn); atomicMax(&s.mx, mx); }
+            __syncthreads();
+            L = s.mn;
+            span = (unsigned)s.mx - L;
+            have = true;
+        }
+        const int shift = max(0, 32 - __clz(span) - kSelCtaBits);       // span >> shift < 4,096
+        span |= (1u << shift) - 1u;                         // the last bin in full: the bins tile the bracket exactly
+        unsigned below = 0u;
+#pragma unroll
+        for (int i = 0; i < 4 * V; ++i) {
+            const unsigned d = key[i] - L;
+            below += d >> 31;                               // key < L (both below 2^31; a pad counts only when L = 0)
+            if (d <= span) atomicAdd(s.hist + (d >> shift), 1u);
+        }
+        if (L == 0u) below = 0u;
+        below = __reduce_add_sync(0xffffffffu, below);
+        if (lane == 0 && below) atomicAdd(&s.below, below);
         __syncthreads();
-        sel_scan_cta_v<NT>(s.hist, k0, (unsigned)((4 - (cols & 3)) & 3), s.tot, s.out);
+        sel_scan_cta_v<NT>(s.hist, k0 - s.below, s.tot, s.out);          // a rank below the bracket wraps: not found
         const unsigned b = s.out[0], kin = s.out[1], hb = s.out[2];
-        prefix |= b << shift;
+        if (hb == 0u) {                                     // the median is outside the sampled bracket
+            if (attempt > 8) break;                         // (cannot happen with the extremes as the bracket)
+            have = false;
+            continue;
+        }
+        const unsigned base = L + (b << shift);             // the bin = keys [base, base + 2^shift)
         bool second_above = even && kin + 1u >= hb;         // the next order statistic lies above this bin
         if (shift == 0) {
-            v1 = v2 = prefix;
+            v1 = v2 = base;
         } else if (hb <= (unsigned)NT) {
             // the bin's keys -> shared memory; rank k of them = the largest key with at most k keys below it
-            const unsigned fmask = (dmask << shift) | 0x80000000u, fval = b << shift;
+            const unsigned width = 1u << shift;
 #pragma unroll
             for (int i = 0; i < 4 * V; ++i)
-                if ((key[i] & fmask) == fval) s.cand[atomicAdd(&s.ncand, 1u)] = key[i];
+                if (key[i] - base < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[i];
             __syncthreads();
             if ((unsigned)(tid & ~31) < hb) {               // warps that own a candidate
-                const unsigned my = (unsigned)tid < hb ? s.cand[tid] : 0u;
+                const bool mine = (unsigned)tid < hb;
+                const unsigned my = mine ? s.cand[tid] : 0u;
                 unsigned lt = 0u;
 #pragma unroll 4
                 for (unsigned i = 0; i < hb; ++i) lt += (s.cand[i] - my) >> 31;       // keys < 2^31: x < my <=> borrow
-                const bool mine = (unsigned)tid < hb;
                 const unsigned a1 = __reduce_max_sync(0xffffffffu, mine && lt <= kin ? my : 0u);
                 const unsigned a2 = __reduce_max_sync(0xffffffffu, mine && lt <= kin + 1u ? my : 0u);
                 if (lane == 0) { atomicMax(&s.v1, a1); atomicMax(&s.v2, a2); }
@@ -308,45 +362,13 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
             __syncthreads();
             v1 = s.v1;
             v2 = s.v2;
-        } else {
-            // heavy ties: more keys in the bin than threads - the remaining digits by histogram passes
-            unsigned k = kin;
-            remaining = shift;
-#pragma unroll 1
-            while (remaining > 0) {
-                const int wd2 = min(kSelCtaBits, remaining), shift2 = remaining - wd2;
-                const unsigned dmask2 = (1u << wd2) - 1u;
-                const unsigned above = (0xffffffffu << remaining) | 0x80000000u;       // bits fixed so far + the pad bit
-#pragma unroll
-                for (int i = 0; i < kSelCtaBins / 4 / NT; ++i) h4[tid + NT * i] = make_uint4(0u, 0u, 0u, 0u);
-                __syncthreads();
-#pragma unroll
-                for (int i = 0; i < 4 * V; ++i)
-                    if (((key[i] ^ prefix) & above) == 0u) atomicAdd(s.hist + ((key[i] >> shift2) & dmask2), 1u);
-                __syncthreads();
-                sel_scan_cta_v<NT>(s.hist, k, 0u, s.tot, s.out);
-                prefix |= s.out[0] << shift2;
-                k = s.out[1];
-                remaining = shift2;
-                __syncthreads();
-            }
-            v1 = prefix;
-            if (even) {                                     // as the kernel above: count <= v1, smallest key above it
-                unsigned cnt = 0u, gt = 0xffffffffu;
-#pragma unroll
-                for (int i = 0; i < 4 * V; ++i) {
-                    if (key[i] <= v1) ++cnt; else gt = min(gt, key[i]);
-                }
-                cnt = __reduce_add_sync(0xffffffffu, cnt);
-                gt = __reduce_min_sync(0xffffffffu, gt);
-                if (lane == 0) { atomicAdd(&s.cnt_le, cnt); atomicMin(&s.min_gt, gt); }
-                __syncthreads();
-                v2 = s.cnt_le >= k0 + 2u ? v1 : s.min_gt;
-            }
-            second_above = false;
+        } else {                                            // heavy ties: the bin is the next bracket
+            L = base;
+            span = (1u << shift) - 1u;
+            continue;
         }
         if (second_above) {                                 // smallest key above the bin (the pad value is above all)
-            const unsigned lim = ((prefix >> shift) + 1u) << shift;
+            const unsigned lim = base + (1u << shift);
             unsigned gt = 0xffffffffu;
 #pragma unroll
             for (int i = 0; i < 4 * V; ++i)
@@ -356,6 +378,7 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
             __syncthreads();
             v2 = s.min_gt;
         }
+        break;
     }
     const float a = __uint_as_float(w.amax[item]);
     float med = __fdiv_rn(__uint_as_float(v1), a);

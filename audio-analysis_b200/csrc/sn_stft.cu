@@ -69,6 +69,140 @@ __device__ __forceinline__ unsigned frame_median_bits(const float (&v)[64], floa
     return prefix;
 }
 
+#if !CAC_SN_COLSEL_RADIX
+// The same median through a sampled bracket (the idea of sn_rowmed_mask_vec_kernel at warp level): `samp` = 32 of the
+// frame's magnitudes spread over the spectrum (one per lane), sorted with shuffles; ranks 6 and 25 bracket the median
+// of all but one frame in about a thousand.  ONE pass then counts the keys below the bracket and puts the keys inside
+// it into a 2,048-bin histogram that spans exactly the bracket ((key - L) >> shift), the bin that holds rank 1024 has
+// one to three keys, they go to shared memory and are ranked by counting.  The counts are exact whatever the bracket;
+// when the rank is outside it the pass is redone with the frame's extremes, a bin of more than 32 keys (ties) becomes
+// the next bracket.  About half the instructions of the three radix passes above.
+__device__ __forceinline__ unsigned sorted_lane(unsigned x, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const unsigned y = __shfl_xor_sync(0xffffffffu, x, j);
+            const bool keep_min = ((lane & j) == 0) == ((lane & k) == 0);
+            x = keep_min ? min(x, y) : max(x, y);
+        }
+    }
+    return x;
+}
+
+// bin of the warp's 2,048-bin histogram that holds rank k -> returned, k becomes the rank inside it, cnt the bin's
+// count; 0xffffffff when k is not below the histogram's total.  All 32 lanes call.
+__device__ __forceinline__ unsigned sel_scan_warp_total(const unsigned* hist, int lane, unsigned& k, unsigned& cnt) {
+    const uint4* h4 = reinterpret_cast<const uint4*>(hist);
+    constexpr int J = kSelWarpBins / 4 / 32;            // 16 quads per lane
+    unsigned c[J];
+    int js = 0;
+    unsigned kk = k;
+    bool found = false;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const uint4 q = h4[lane + 32 * j];
+        c[j] = q.x + q.y + q.z + q.w;
+        const unsigned t = __reduce_add_sync(0xffffffffu, c[j]);     // bins [128 j, 128 j + 128)
+        if (!found) {
+            if (kk >= t) { kk -= t; js = j + 1; } else found = true;
+        }
+    }
+    if (!found) return 0xffffffffu;
+    unsigned cj = c[0];
+#pragma unroll
+    for (int j = 1; j < J; ++j)
+        if (js == j) cj = c[j];
+    unsigned inc = cj;                                   // inclusive prefix over the lanes of block js
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+    }
+    const unsigned ball = __ballot_sync(0xffffffffu, inc > kk);
+    const int ls = __ffs(ball) - 1;                      // kk < the block's total: some lane's prefix exceeds it
+    kk -= __shfl_sync(0xffffffffu, inc - cj, ls);
+    const uint4 q = h4[ls + 32 * js];                    // the quad that holds the rank (same address for all lanes)
+    unsigned b = 0, n = q.x;
+    if (kk >= q.x) { kk -= q.x; b = 1; n = q.y; if (kk >= q.y) { kk -= q.y; b = 2; n = q.z; if (kk >= q.z) { kk -= q.z; b = 3; n = q.w; } } }
+    k = kk;
+    cnt = n;
+    return 4u * (unsigned)(ls + 32 * js) + b;
+}
+
+__device__ __forceinline__ unsigned frame_median_bracketed(const float (&v)[64], float nyq, float samp, unsigned mxkey,
+                                                           unsigned* hist, int lane) {
+    uint4* h4 = reinterpret_cast<uint4*>(hist);
+    unsigned* trash = hist + kSelWarpBins + lane;         // the warp's buffer has 2,112 words: 32 spare ones per lane
+    const unsigned ekey = __float_as_uint(nyq);
+    unsigned L, span;
+    {
+        const unsigned x = sorted_lane(__float_as_uint(samp), lane);
+        L = __shfl_sync(0xffffffffu, x, 6);
+        span = __shfl_sync(0xffffffffu, x, 25) - L;
+    }
+#pragma unroll 1
+    for (int attempt = 0; attempt < 12; ++attempt) {
+#pragma unroll
+        for (int j = 0; j < kSelWarpBins / 4 / 32; ++j) h4[lane + 32 * j] = make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();
+        const int shift = max(0, 32 - __clz(span) - kSelWarpBits);     // span >> shift < 2,048
+        span |= (1u << shift) - 1u;                         // the last bin in full: the bins tile the bracket exactly
+        unsigned below = 0u;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+            const unsigned d = __float_as_uint(v[i]) - L;
+            below += d >> 31;                               // key < L: both are below 2^31
+            smem_inc_sel(hist, d >> shift, d <= span, trash);
+        }
+        if (lane == 0) {
+            const unsigned d = ekey - L;
+            below += d >> 31;
+            smem_inc_sel(hist, d >> shift, d <= span, trash);
+        }
+        __syncwarp();
+        below = __reduce_add_sync(0xffffffffu, below);
+        unsigned k = 1024u - below, hb = 0u;                // a rank below the bracket wraps: not found
+        const unsigned digit = sel_scan_warp_total(hist, lane, k, hb);
+        __syncwarp();                                       // every lane has read the histogram before it is reused
+        if (digit == 0xffffffffu) {                         // the median is outside the sampled bracket: the extremes
+            float mn = nyq;
+#pragma unroll
+            for (int i = 0; i < 64; ++i) mn = fminf(mn, v[i]);
+            L = __float_as_uint(warp_min(mn));
+            span = mxkey - L;
+            continue;
+        }
+        const unsigned base = L + (digit << shift);
+        if (shift == 0) return base;
+        const unsigned width = 1u << shift;
+        if (hb > 32u) {                                     // ties: the bin is the next bracket
+            L = base;
+            span = width - 1u;
+            continue;
+        }
+        // the bin's keys -> hist[0..31] (counter in hist[32]); rank k = the largest with at most k keys below it
+        if (lane == 0) hist[32] = 0u;
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+            const unsigned key = __float_as_uint(v[i]);
+            if (key - base < width) hist[atomicAdd(hist + 32, 1u)] = key;
+        }
+        if (lane == 0 && ekey - base < width) hist[atomicAdd(hist + 32, 1u)] = ekey;
+        __syncwarp();
+        const bool mine = (unsigned)lane < hb;
+        const unsigned my = mine ? hist[lane] : 0u;
+        unsigned lt = 0u;
+        for (unsigned i = 0; i < hb; ++i) lt += (__shfl_sync(0xffffffffu, my, (int)i) - my) >> 31;
+        const unsigned r = __reduce_max_sync(0xffffffffu, mine && lt <= k ? my : 0u);
+        __syncwarp();
+        return r;
+    }
+    return 0u;                                              // not reached: the extremes always hold the rank
+}
+#endif
+
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const float* __restrict__ pcm, const SnWave w,
                                                                        int hop, int fps, int stage_half) {
     extern __shared__ __align__(16) float smem[];
@@ -141,7 +275,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
             const int fi = r0 + warp;
             const bool active = fi < nfs;
             float v[64];
-            float nyq = 0.f;
+            float nyq = 0.f, samp = 0.f;
             if (active) {
 #if CAC_FFT_PACKED
                 fft_frame_p<1, 32, true>(se, so, fi * hop, ex, pbuf, lane, lt);
@@ -152,6 +286,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
 #pragma unroll
                 for (int i = 0; i < 64; ++i) v[i] = pbuf[lane + 32 * i];     // the lane's own values, 2 |X[k]|
                 nyq = pbuf[2048];
+#if !CAC_SN_COLSEL_RADIX
+                samp = pbuf[64 * lane + 21];                                  // 32 magnitudes spread over the spectrum
+#endif
             }
             __syncthreads();                   // the round's magnitudes are complete in the 12 buffers
             {
@@ -176,6 +313,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
             }
             __syncthreads();                   // the buffers are free: they become the histograms
             if (active) {
+#if CAC_SN_COLSEL_RADIX
                 float mx = nyq, mn = nyq;
 #pragma unroll
                 for (int i = 0; i < 64; ++i) { mx = fmaxf(mx, v[i]); mn = fminf(mn, v[i]); }
@@ -183,6 +321,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
                 mn = warp_min(mn);
                 vmax = fmaxf(vmax, mx);
                 const unsigned med = frame_median_bits(v, nyq, __float_as_uint(mn), __float_as_uint(mx), hist, lane);
+#else
+                float mx = nyq;
+#pragma unroll
+                for (int i = 0; i < 64; ++i) mx = fmaxf(mx, v[i]);
+                mx = warp_max(mx);
+                vmax = fmaxf(vmax, mx);
+                const unsigned med = frame_median_bracketed(v, nyq, samp, __float_as_uint(mx), hist, lane);
+#endif
                 if (lane == 0) colmed[f0 + fi] = 0.5f * __uint_as_float(med);
             }
         }
