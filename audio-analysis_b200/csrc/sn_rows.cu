@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_kernel(const SnWave w
 constexpr unsigned kNoKey = 0x80000000u;      // -0.0f: above every magnitude as unsigned, below as signed, never > t
 
 struct RowSelV {
-    unsigned hist[kSelCtaBins];
+    unsigned hist[kSelCtaBins + 32];          // + one overflow word per lane: keys outside the bracket
     unsigned tot[32];
     unsigned out[4];                          // bin, rank inside the bin, keys in the bin (0: rank not in the histogram)
     unsigned mn;
@@ -322,10 +322,10 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
         span |= (1u << shift) - 1u;                         // the last bin in full: the bins tile the bracket exactly
         unsigned below = 0u;
 #pragma unroll
-        for (int i = 0; i < 4 * V; ++i) {
-            const unsigned d = key[i] - L;
+        for (int i = 0; i < 4 * V; ++i) {                   // no branch: a key outside the bracket (below: d wraps) is
+            const unsigned d = key[i] - L;                  // clamped to the lane's overflow word
             below += d >> 31;                               // key < L (both below 2^31; a pad counts only when L = 0)
-            if (d <= span) atomicAdd(s.hist + (d >> shift), 1u);
+            atomicAdd(s.hist + min(d >> shift, (unsigned)(kSelCtaBins + lane)), 1u);
         }
         if (L == 0u) below = 0u;
         below = __reduce_add_sync(0xffffffffu, below);
@@ -346,8 +346,15 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
             // the bin's keys -> shared memory; rank k of them = the largest key with at most k keys below it
             const unsigned width = 1u << shift;
 #pragma unroll
-            for (int i = 0; i < 4 * V; ++i)
-                if (key[i] - base < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[i];
+            for (int v = 0; v < V; ++v) {                   // one branch per four keys: a hit is rare
+                const unsigned e0 = key[4 * v] - base, e1 = key[4 * v + 1] - base, e2 = key[4 * v + 2] - base, e3 = key[4 * v + 3] - base;
+                if (min(min(e0, e1), min(e2, e3)) < width) {
+                    if (e0 < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[4 * v];
+                    if (e1 < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[4 * v + 1];
+                    if (e2 < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[4 * v + 2];
+                    if (e3 < width) s.cand[atomicAdd(&s.ncand, 1u)] = key[4 * v + 3];
+                }
+            }
             __syncthreads();
             if ((unsigned)(tid & ~31) < hb) {               // warps that own a candidate
                 const bool mine = (unsigned)tid < hb;
@@ -369,14 +376,13 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
         }
         if (second_above) {                                 // smallest key above the bin (the pad value is above all)
             const unsigned lim = base + (1u << shift);
-            unsigned gt = 0xffffffffu;
+            unsigned gt = 0xffffffffu;                      // min of key - lim over the keys >= lim (the others wrap high)
 #pragma unroll
-            for (int i = 0; i < 4 * V; ++i)
-                if (key[i] >= lim) gt = min(gt, key[i]);
+            for (int i = 0; i < 4 * V; ++i) gt = min(gt, key[i] - lim);
             gt = __reduce_min_sync(0xffffffffu, gt);
             if (lane == 0) atomicMin(&s.min_gt, gt);
             __syncthreads();
-            v2 = s.min_gt;
+            v2 = s.min_gt + lim;
         }
         break;
     }

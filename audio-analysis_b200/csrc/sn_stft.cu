@@ -132,8 +132,7 @@ __device__ __forceinline__ unsigned sel_scan_warp_total(const unsigned* hist, in
 
 __device__ __forceinline__ unsigned frame_median_bracketed(const float (&v)[64], float nyq, float samp, unsigned mxkey,
                                                            unsigned* hist, int lane) {
-    uint4* h4 = reinterpret_cast<uint4*>(hist);
-    unsigned* trash = hist + kSelWarpBins + lane;         // the warp's buffer has 2,112 words: 32 spare ones per lane
+    uint4* h4 = reinterpret_cast<uint4*>(hist);           // the warp's buffer has 2,112 words: 32 spare ones per lane
     const unsigned ekey = __float_as_uint(nyq);
     unsigned L, span;
     {
@@ -151,14 +150,14 @@ __device__ __forceinline__ unsigned frame_median_bracketed(const float (&v)[64],
         unsigned below = 0u;
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
-            const unsigned d = __float_as_uint(v[i]) - L;
+            const unsigned d = __float_as_uint(v[i]) - L;   // outside the bracket (below: d wraps): the lane's spare word
             below += d >> 31;                               // key < L: both are below 2^31
-            smem_inc_sel(hist, d >> shift, d <= span, trash);
+            atomicAdd(hist + min(d >> shift, (unsigned)(kSelWarpBins + lane)), 1u);
         }
         if (lane == 0) {
             const unsigned d = ekey - L;
             below += d >> 31;
-            smem_inc_sel(hist, d >> shift, d <= span, trash);
+            atomicAdd(hist + min(d >> shift, (unsigned)kSelWarpBins), 1u);
         }
         __syncwarp();
         below = __reduce_add_sync(0xffffffffu, below);
@@ -185,9 +184,15 @@ __device__ __forceinline__ unsigned frame_median_bracketed(const float (&v)[64],
         if (lane == 0) hist[32] = 0u;
         __syncwarp();
 #pragma unroll
-        for (int i = 0; i < 64; ++i) {
-            const unsigned key = __float_as_uint(v[i]);
-            if (key - base < width) hist[atomicAdd(hist + 32, 1u)] = key;
+        for (int i = 0; i < 64; i += 4) {                   // one branch per four keys: a hit is rare
+            const unsigned e0 = __float_as_uint(v[i]) - base, e1 = __float_as_uint(v[i + 1]) - base;
+            const unsigned e2 = __float_as_uint(v[i + 2]) - base, e3 = __float_as_uint(v[i + 3]) - base;
+            if (min(min(e0, e1), min(e2, e3)) < width) {
+                if (e0 < width) hist[atomicAdd(hist + 32, 1u)] = e0 + base;
+                if (e1 < width) hist[atomicAdd(hist + 32, 1u)] = e1 + base;
+                if (e2 < width) hist[atomicAdd(hist + 32, 1u)] = e2 + base;
+                if (e3 < width) hist[atomicAdd(hist + 32, 1u)] = e3 + base;
+            }
         }
         if (lane == 0 && ekey - base < width) hist[atomicAdd(hist + 32, 1u)] = ekey;
         __syncwarp();
