@@ -217,6 +217,7 @@ extern "C" int cac_signal_components_run(const float* d_spec, int32_t rows, int6
                                          void* d_work, size_t work_bytes, void* stream) {
     if (!d_spec || !d_result || !d_work) return fail(CAC_ERR_INVALID, "null argument");
     if (rows < 1 || cols < 1 || (int64_t)rows * cols > 0x7fffffffLL) return fail(CAC_ERR_INVALID, "matrix size out of range");
+    if (rows > 65535) return fail(CAC_ERR_INVALID, "more than 65,535 rows (rows ride on a grid dimension)");
     if (max_components < 1) return fail(CAC_ERR_INVALID, "max_components out of range");
     int rc = check_morph(dilate_h, dilate_w, erode_h);
     if (rc) return rc;

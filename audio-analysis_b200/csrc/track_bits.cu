@@ -12,87 +12,97 @@
 
 namespace cac {
 
-__device__ __forceinline__ unsigned valid_bits(int w, long long cols) {   // pixels of word w that exist
-    const long long left = cols - 32LL * w;
-    return left >= 32 ? 0xffffffffu : (left <= 0 ? 0u : ((1u << (int)left) - 1u));
+__device__ __forceinline__ unsigned valid_bits(int w, int cols) {          // pixels of word w that exist
+    const int left = cols - 32 * w;
+    return left >= 32 ? 0xffffffffu : (left <= 0 ? 0u : ((1u << left) - 1u));
 }
 
 // ---- cv2.erode / cv2.dilate with a 1 x k rectangle: out(x) = OR | AND over d in [0, k) of in(x - k/2 + d) ----
 // pixels outside the image are ignored (cv2's morphology border).  Erosion runs as the complement of the
 // dilation of the complement (outside = 0 in the complemented domain is exactly "ignored").
-// One thread per output word, (row, word) flattened so that every CTA is full whatever the row length; the two or
-// three input words a thread needs come straight from L1 / L2 (the whole mask plane is 2.6 MB).
+// A thread owns ONE word column of a strip of kMorphStrip rows (grid: word chunks x strips x recordings): no index
+// division, the per-thread set-up is paid once per strip, and the two to four input words an output needs (and, in the
+// vertical pass, the k rows) come from L1 / L2 - the whole mask plane of a recording is 2.6 MB.  (The first version
+// ran one thread per output word with a 64-bit division to find its row: ~150 instructions of overhead for ~20 of
+// work, 70 us for the 1 x 1 "copy" pass of a wave.)
+constexpr int kMorphStrip = 8, kMorphThreads = 128;
+
 template <bool IS_MAX>
-__device__ __forceinline__ unsigned morph_word(const unsigned* row, int w, int wpr, long long cols) {
+__device__ __forceinline__ unsigned morph_word(const unsigned* row, int w, int wpr, int cols) {
     if (w < 0 || w >= wpr) return 0u;
     const unsigned v = __ldg(row + w);
     return IS_MAX ? v : (~v & valid_bits(w, cols));
 }
 template <bool IS_MAX>
-__global__ void __launch_bounds__(256) morph_h_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
+__global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     const SnItem im = wv.items[blockIdx.z];
-    const int wpr = im.wpr;
-    const long long cols = im.cols;
-    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (idx >= (long long)wv.rows * wpr) return;
-    const int r = (int)(idx / wpr), w = (int)(idx - (long long)r * wpr);
+    const int wpr = im.wpr, cols = im.cols;
+    const int w = blockIdx.x * kMorphThreads + threadIdx.x;
+    if (w >= wpr) return;
     const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
     unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
-    const unsigned* row = in + (size_t)r * wpr;
+    const unsigned vb = valid_bits(w, cols);
     // out = OR over d in [0, k) of the 32-pixel window starting at pixel 32 w - anchor + d
-    int bit = 32 * w - k / 2;                              // may be negative: arithmetic shift = floor division
-    int i = bit >> 5;
-    unsigned acc = 0u;
-    if (k <= 64) {
-        // the windows all lie inside words i .. i + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
-        // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k
-        unsigned A[5];
+    const int bit0 = 32 * w - k / 2;                       // may be negative: arithmetic shift = floor division
+    const int i0 = bit0 >> 5;
+    const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, wv.rows);
+    for (int r = r_begin; r < r_end; ++r) {
+        const unsigned* row = in + (size_t)r * wpr;
+        unsigned acc = 0u;
+        if (k <= 64) {
+            // the windows all lie inside words i .. i + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
+            // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k
+            unsigned A[5];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) A[j] = morph_word<IS_MAX>(row, i + j, wpr, cols);
-        A[4] = 0u;
-        int m = 1;
-        for (; 2 * m <= k; m <<= 1) {
+            for (int j = 0; j < 4; ++j) A[j] = morph_word<IS_MAX>(row, i0 + j, wpr, cols);
+            A[4] = 0u;
+            int m = 1;
+            for (; 2 * m <= k; m <<= 1) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
-        }
-        const int rest = k - m;                            // < m <= 32
-        if (rest) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
-        }
-        acc = __funnelshift_rc(A[0], A[1], bit & 31);
-    } else {
-        unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
-        for (int d = 0; d < k; ++d, ++bit) {
-            if ((bit >> 5) != i) {
-                i = bit >> 5;
-                lo = hi;
-                hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+                for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
             }
-            acc |= __funnelshift_r(lo, hi, bit & 31);
+            const int rest = k - m;                        // < m <= 32
+            if (rest) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
+            }
+            acc = __funnelshift_rc(A[0], A[1], bit0 & 31);
+        } else {
+            int bit = bit0, i = i0;
+            unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+            for (int d = 0; d < k; ++d, ++bit) {
+                if ((bit >> 5) != i) {
+                    i = bit >> 5;
+                    lo = hi;
+                    hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+                }
+                acc |= __funnelshift_r(lo, hi, bit & 31);
+            }
         }
+        if (!IS_MAX) acc = ~acc;
+        out[(size_t)r * wpr + w] = acc & vb;
     }
-    if (!IS_MAX) acc = ~acc;
-    out[(size_t)r * wpr + w] = acc & valid_bits(w, cols);
 }
 
 // ---- k x 1 rectangle: OR | AND over the rows r - k/2 .. r - k/2 + k - 1 that exist --------------------
 template <bool IS_MAX>
-__global__ void __launch_bounds__(256) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
+__global__ void __launch_bounds__(kMorphThreads) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     const int wpr = wv.items[blockIdx.z].wpr;
     const int rows = wv.rows;
-    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (idx >= (long long)rows * wpr) return;
-    const int r = (int)(idx / wpr), w = (int)(idx - (long long)r * wpr);
-    const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride;
-    unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride;
-    const int r0 = max(r - k / 2, 0), r1 = min(r - k / 2 + k - 1, rows - 1);
-    unsigned acc = IS_MAX ? 0u : 0xffffffffu;        // AND of real rows keeps the (zero) padding bits zero
-    for (int rr = r0; rr <= r1; ++rr) {
-        const unsigned v = __ldg(in + (size_t)rr * wpr + w);
-        acc = IS_MAX ? (acc | v) : (acc & v);
+    const int w = blockIdx.x * kMorphThreads + threadIdx.x;
+    if (w >= wpr) return;
+    const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride + w;
+    unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride + w;
+    const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, rows);
+    for (int r = r_begin; r < r_end; ++r) {
+        const int r0 = max(r - k / 2, 0), r1 = min(r - k / 2 + k - 1, rows - 1);
+        unsigned acc = IS_MAX ? 0u : 0xffffffffu;    // AND of real rows keeps the (zero) padding bits zero
+        for (int rr = r0; rr <= r1; ++rr) {
+            const unsigned v = __ldg(in + (size_t)rr * wpr);
+            acc = IS_MAX ? (acc | v) : (acc & v);
+        }
+        out[(size_t)r * wpr] = acc;
     }
-    out[idx] = acc;
 }
 
 __global__ void __launch_bounds__(256) unpack_bits_kernel(const SnWave wv, int plane, unsigned char* __restrict__ out_all,
@@ -274,14 +284,15 @@ __global__ void __launch_bounds__(256) stats_init_kernel(const SnWave wv) {
 // out = erode (is_max = false) / dilate (true) of plane `src` with a kh x kw rectangle; `tmp` is scratch
 cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp_plane, int dst_plane, int max_wpr, int kh,
                                          int kw, bool is_max, cudaStream_t st) {
-    const long long words = (long long)w.rows * max_wpr;
-    dim3 grid((unsigned)((words + 255) / 256), 1, (unsigned)w.n_items);
+    // (rows ride on grid.y here and in the component kernels: matrices of up to 65,535 rows)
+    dim3 grid((unsigned)((max_wpr + kMorphThreads - 1) / kMorphThreads), (unsigned)((w.rows + kMorphStrip - 1) / kMorphStrip),
+              (unsigned)w.n_items);
     if (is_max) {
-        morph_h_bits_kernel<true><<<grid, 256, 0, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<true><<<grid, 256, 0, st>>>(w, tmp_plane, dst_plane, kh);
+        morph_h_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);
     } else {
-        morph_h_bits_kernel<false><<<grid, 256, 0, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<false><<<grid, 256, 0, st>>>(w, tmp_plane, dst_plane, kh);
+        morph_h_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
+        morph_v_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);
     }
     return cudaGetLastError();
 }

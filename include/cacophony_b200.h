@@ -271,7 +271,8 @@ int cac_sn_spectrum_run(cac_sn_plan* plan, const float* d_pcm, int64_t n_samples
 /* The stages after the STFT (:658-686) on a spectrogram the caller supplies: d_spec [rows][cols] = spectogram / a_max.
  * Same kernels as cac_sn_run behind the column medians (taken through a transpose here).  d_result as above for one
  * recording; d_stage_masks (may be NULL) receives the three uint8 [rows][cols] masks (threshold, opened, closed).
- * d_work: cac_signal_components_work_bytes(rows, cols) bytes, 256-byte aligned.  Neither allocates nor synchronises. */
+ * d_work: cac_signal_components_work_bytes(rows, cols) bytes, 256-byte aligned.  Neither allocates nor synchronises.
+ * rows <= 65,535, rows * cols < 2^31. */
 size_t cac_signal_components_work_bytes(int32_t rows, int64_t cols);
 int cac_signal_components_run(const float* d_spec, int32_t rows, int64_t cols, int32_t dilate_h, int32_t dilate_w,
                               int32_t erode_h, int32_t max_components, int32_t* d_result, uint8_t* d_stage_masks,

@@ -81,6 +81,26 @@ def test_row_medians_exact_on_16_byte_aligned_rows(engine, shape):
     assert len(bad) == 0, (shape, bad[:5])
 
 
+@pytest.mark.parametrize("shape,dh,dw,eh", [((60001, 8), 10, 3, 1), ((37, 700), 7, 70, 2), ((300, 33), 1, 1, 0)])
+def test_morphology_on_other_shapes_follows_cv2(engine, shape, dh, dw, eh):
+    """The strip kernels on matrices unlike the fused chain's: 60,001 rows (a last strip of one row), a structuring
+    element wider than 64 pixels, rows shorter than two words, erode height 0 (3 x 3)."""
+    import cv2
+    import torch
+    rng = np.random.default_rng(shape[0])
+    x = np.abs(rng.standard_normal(shape)).astype(np.float32)
+    blocks = rng.random(((shape[0] + 5) // 6, (shape[1] + 4) // 5)) < 0.3      # 6 x 5 blobs survive the 4 x 4 opening
+    x[np.kron(blocks, np.ones((6, 5), bool))[: shape[0], : shape[1]]] += 40.0
+    _, masks = engine.signal_components(torch.from_numpy(x).cuda(), dh, dw, eh, max_components=1 << 20, want_masks=True)
+    masks = masks.cpu().numpy()
+    opened = cv2.morphologyEx(masks[0], cv2.MORPH_OPEN, np.ones((4, 4), np.uint8))
+    closed = cv2.dilate(opened, np.ones((dh, dw), np.uint8))
+    closed = cv2.erode(closed, np.ones((eh, dw) if eh else (3, 3), np.uint8))
+    assert masks[0].any() and opened.any()
+    assert np.array_equal(masks[1], opened)
+    assert np.array_equal(masks[2], closed)
+
+
 @pytest.mark.parametrize("name,seed,seconds", CASES)
 def test_signal_noise_equals_reference_fixture(engine, golden, name, seed, seconds):
     from audio_analysis_b200 import identify_tracks as T
