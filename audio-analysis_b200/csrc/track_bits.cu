@@ -189,13 +189,15 @@ __device__ __forceinline__ CclView ccl_view(const SnWave& wv, int plane) {
 __global__ void __launch_bounds__(128) runs_init_kernel(const SnWave wv, int plane) {
     const CclView v = ccl_view(wv, plane);
     const int w = blockIdx.x * 128 + threadIdx.x;
-    const int y = blockIdx.y;
     if (w >= v.wpr) return;
-    unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
-    while (s) {
-        const int x = 32 * w + __ffs(s) - 1;
-        s &= s - 1;
-        v.label[y * v.cols + x] = y * v.cols + x;
+    const int y_end = min((int)(blockIdx.y + 1) * kMorphStrip, wv.rows);
+    for (int y = blockIdx.y * kMorphStrip; y < y_end; ++y) {
+        unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
+        while (s) {
+            const int x = 32 * w + __ffs(s) - 1;
+            s &= s - 1;
+            v.label[y * v.cols + x] = y * v.cols + x;
+        }
     }
 }
 
@@ -205,28 +207,30 @@ __global__ void __launch_bounds__(128) runs_merge_kernel(const SnWave wv, int pl
     const int wpr = v.wpr, cols = v.cols;
     int* label = v.label;
     const int w = blockIdx.x * 128 + threadIdx.x;
-    const int y = blockIdx.y + 1;
-    if (w >= wpr || y >= wv.rows) return;
-    const unsigned* row = v.bits + (size_t)y * wpr;
-    const unsigned* up = row - wpr;
-    unsigned s = start_bits(row, w);
-    while (s) {
-        const int xs = 32 * w + __ffs(s) - 1;
-        s &= s - 1;
-        const int xe = run_end(row, wpr, xs);
-        const int lo = max(xs - 1, 0), hi = min(xe + 1, cols - 1);
-        int x = lo;
-        while (x <= hi) {
-            // next set pixel of the row above at or after x
-            int uw = x >> 5;
-            unsigned m = up[uw] & (0xffffffffu << (x & 31));
-            while (m == 0u && 32 * (uw + 1) <= hi) m = up[++uw];
-            if (m == 0u) break;
-            const int ux = 32 * uw + __ffs(m) - 1;
-            if (ux > hi) break;
-            const int us = run_start(up, ux);
-            uf_union(label, y * cols + xs, (y - 1) * cols + us);
-            x = run_end(up, wpr, ux) + 2;            // the pixel after a run is clear
+    if (w >= wpr) return;
+    const int y_end = min((int)(blockIdx.y + 1) * kMorphStrip, wv.rows);
+    for (int y = max((int)blockIdx.y * kMorphStrip, 1); y < y_end; ++y) {
+        const unsigned* row = v.bits + (size_t)y * wpr;
+        const unsigned* up = row - wpr;
+        unsigned s = start_bits(row, w);
+        while (s) {
+            const int xs = 32 * w + __ffs(s) - 1;
+            s &= s - 1;
+            const int xe = run_end(row, wpr, xs);
+            const int lo = max(xs - 1, 0), hi = min(xe + 1, cols - 1);
+            int x = lo;
+            while (x <= hi) {
+                // next set pixel of the row above at or after x
+                int uw = x >> 5;
+                unsigned m = up[uw] & (0xffffffffu << (x & 31));
+                while (m == 0u && 32 * (uw + 1) <= hi) m = up[++uw];
+                if (m == 0u) break;
+                const int ux = 32 * uw + __ffs(m) - 1;
+                if (ux > hi) break;
+                const int us = run_start(up, ux);
+                uf_union(label, y * cols + xs, (y - 1) * cols + us);
+                x = run_end(up, wpr, ux) + 2;        // the pixel after a run is clear
+            }
         }
     }
 }
@@ -236,13 +240,15 @@ __global__ void __launch_bounds__(128) runs_merge_kernel(const SnWave wv, int pl
 __global__ void __launch_bounds__(128) runs_roots_kernel(const SnWave wv, int plane) {
     const CclView v = ccl_view(wv, plane);
     const int w = blockIdx.x * 128 + threadIdx.x;
-    const int y = blockIdx.y;
     if (w >= v.wpr) return;
-    unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
-    while (s) {
-        const int p = y * v.cols + 32 * w + __ffs(s) - 1;
-        s &= s - 1;
-        if (v.label[p] == p) v.label[p] = -1 - atomicAdd(v.result, 1);
+    const int y_end = min((int)(blockIdx.y + 1) * kMorphStrip, wv.rows);
+    for (int y = blockIdx.y * kMorphStrip; y < y_end; ++y) {
+        unsigned s = start_bits(v.bits + (size_t)y * v.wpr, w);
+        while (s) {
+            const int p = y * v.cols + 32 * w + __ffs(s) - 1;
+            s &= s - 1;
+            if (v.label[p] == p) v.label[p] = -1 - atomicAdd(v.result, 1);
+        }
     }
 }
 
@@ -251,23 +257,25 @@ __global__ void __launch_bounds__(128) runs_stats_kernel(const SnWave wv, int pl
     const CclView v = ccl_view(wv, plane);
     const int wpr = v.wpr, cols = v.cols;
     const int w = blockIdx.x * 128 + threadIdx.x;
-    const int y = blockIdx.y;
     if (w >= wpr) return;
-    const unsigned* row = v.bits + (size_t)y * wpr;
-    unsigned s = start_bits(row, w);
-    while (s) {
-        const int xs = 32 * w + __ffs(s) - 1;
-        s &= s - 1;
-        const int xe = run_end(row, wpr, xs);
-        const int id = uf_find_id(v.label, y * cols + xs);
-        if (id >= wv.max_components) continue;
-        int* st = v.result + 4 + 6 * id;
-        atomicMin(st + 0, xs);
-        atomicMin(st + 1, y);
-        atomicMax(st + 2, xe);
-        atomicMax(st + 3, y);
-        atomicAdd(st + 4, xe - xs + 1);
-        atomicMin(st + 5, (y >> 1) * ((cols + 1) >> 1) + (xs >> 1));
+    const int y_end = min((int)(blockIdx.y + 1) * kMorphStrip, wv.rows);
+    for (int y = blockIdx.y * kMorphStrip; y < y_end; ++y) {
+        const unsigned* row = v.bits + (size_t)y * wpr;
+        unsigned s = start_bits(row, w);
+        while (s) {
+            const int xs = 32 * w + __ffs(s) - 1;
+            s &= s - 1;
+            const int xe = run_end(row, wpr, xs);
+            const int id = uf_find_id(v.label, y * cols + xs);
+            if (id >= wv.max_components) continue;
+            int* st = v.result + 4 + 6 * id;
+            atomicMin(st + 0, xs);
+            atomicMin(st + 1, y);
+            atomicMax(st + 2, xe);
+            atomicMax(st + 3, y);
+            atomicAdd(st + 4, xe - xs + 1);
+            atomicMin(st + 5, (y >> 1) * ((cols + 1) >> 1) + (xs >> 1));
+        }
     }
 }
 
@@ -305,14 +313,12 @@ cudaError_t launch_unpack_bits_batch(const SnWave& w, int plane, unsigned char* 
 }
 
 cudaError_t launch_ccl_runs_batch(const SnWave& w, int plane, int max_wpr, cudaStream_t st) {
-    dim3 grid((unsigned)((max_wpr + 127) / 128), (unsigned)w.rows, (unsigned)w.n_items);
+    // a thread owns one word column of a strip of kMorphStrip rows, as in the morphology kernels
+    dim3 grid((unsigned)((max_wpr + 127) / 128), (unsigned)((w.rows + kMorphStrip - 1) / kMorphStrip), (unsigned)w.n_items);
     const int init_n = w.max_components > 4 ? w.max_components : 4;
     stats_init_kernel<<<dim3((unsigned)((init_n + 255) / 256), (unsigned)w.n_items), 256, 0, st>>>(w);
     runs_init_kernel<<<grid, 128, 0, st>>>(w, plane);
-    if (w.rows > 1) {
-        dim3 gridm(grid.x, (unsigned)(w.rows - 1), grid.z);
-        runs_merge_kernel<<<gridm, 128, 0, st>>>(w, plane);
-    }
+    if (w.rows > 1) runs_merge_kernel<<<grid, 128, 0, st>>>(w, plane);
     runs_roots_kernel<<<grid, 128, 0, st>>>(w, plane);
     runs_stats_kernel<<<grid, 128, 0, st>>>(w, plane);
     return cudaGetLastError();
