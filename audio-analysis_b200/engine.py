@@ -95,6 +95,7 @@ lib.cac_signal_components_run.argtypes = [_vp, _i32, _i64, _i32, _i32, _i32, _i3
 lib.cac_get_end_work_bytes.argtypes = [_vp, _i64, _i64, _i32]
 lib.cac_get_end_work_bytes.restype = ctypes.c_size_t
 lib.cac_get_end_run.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _vp, _vp, ctypes.c_size_t, _vp]
+lib.cac_tracks_merge.argtypes = [_vp, _i32, _vp, ctypes.POINTER(ctypes.c_int32)]
 lib.cac_host_register.argtypes = [_vp, ctypes.c_size_t]
 lib.cac_host_unregister.argtypes = [_vp]
 lib.cac_magtransform_run.argtypes = [_vp, _vp, _i64, ctypes.c_float, _vp]
@@ -109,7 +110,7 @@ EXPORTS = ["cac_resample_plan_create", "cac_resample_plan_destroy", "cac_resampl
            "cac_scale_by_max_run", "cac_chunk_minmax_run", "cac_morepork_windows_run", "cac_ci_plan_create", "cac_ci_plan_destroy", "cac_ci_window_count", "cac_ci_bins_run", "cac_ci_run",
            "cac_ci_host", "cac_ci_entries_run", "cac_version", "cac_last_error", "cac_device_count", "cac_plan_create", "cac_plan_destroy",
            "cac_plan_frames", "cac_measure_fp32_tflops", "cac_plan_set_magtransform", "cac_plan_set_profiling", "cac_plan_last_kernel_ms", "cac_features_work_bytes", "cac_features_run", "cac_features_host", "cac_features_host_pcm16",
-           "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run", "cac_power_to_db_static"]
+           "cac_normalize_run", "cac_mel_project_run", "cac_power_to_db_run", "cac_power_to_db_static", "cac_tracks_merge"]
 
 
 class CacError(RuntimeError):

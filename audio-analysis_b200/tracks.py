@@ -154,14 +154,39 @@ def merge_signals(signals):
     return survivors, bool(dead)
 
 
+def merge_until_stable(signals):
+    """`while merged: signals, merged = merge_signals(signals)` (src/identify_tracks.py:800-802) through the library's
+    host function cac_tracks_merge: the sweeps run in C on the boxes' float64 values (the same operations in the same
+    order as _should_merge), and every surviving Signal then takes its fields from the ORIGINAL objects the result
+    names - the same objects, types and values the Python loop above leaves behind (merge() only ever takes minima
+    and maxima).  tests/test_tracks_host.py runs both on the golden rectangles and on random ones."""
+    import ctypes
+    from . import engine
+    n = len(signals)
+    if n == 0:
+        return []
+    orig = [(s.start, s.end, s.freq_start, s.freq_end, s.mel_freq_start, s.mel_freq_end) for s in signals]
+    boxes = np.array(orig, dtype=np.float64)
+    out = np.empty((n, 5), dtype=np.int32)
+    n_out = ctypes.c_int32()
+    engine.check(engine.lib.cac_tracks_merge(boxes.ctypes.data, n, out.ctypes.data, ctypes.byref(n_out)))
+    survivors = []
+    for j, (me, i_s, i_e, i_fs, i_fe) in enumerate(out.tolist()):
+        s = signals[me]                                # rows beyond n_out: absorbed signals, as the loop above leaves them
+        s.start, s.end = orig[i_s][0], orig[i_e][1]
+        s.freq_start, s.mel_freq_start = orig[i_fs][2], orig[i_fs][4]
+        s.freq_end, s.mel_freq_end = orig[i_fe][3], orig[i_fe][5]
+        if j < n_out.value:
+            survivors.append(s)
+    return survivors
+
+
 def get_tracks_from_signals(signals, end):
     """src/identify_tracks.py:795-842: merge until nothing merges, drop short signals, enlarge the rest by 1.4x (at
     least 0.7 s, clipped to [0, end]) absorbing signals that overlap more than 70 % of the shorter one, drop tracks
     narrower than 50 mel.  Quirk kept: the minimum length starts at 0.35 s but is overwritten by every overlap test
     with the shorter length of the pair just compared (:803, :826)."""
-    merged = True
-    while merged:
-        signals, merged = merge_signals(signals)
+    signals = merge_until_stable(signals)
     dead = set()
     min_length = 0.35
     for s in signals:

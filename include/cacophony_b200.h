@@ -268,6 +268,18 @@ int cac_sn_run(cac_sn_plan* plan, const float* d_pcm, const int64_t* d_item_offs
 int cac_sn_spectrum_run(cac_sn_plan* plan, const float* d_pcm, int64_t n_samples, float* d_spec, float* d_colmed,
                         float* d_amax, void* d_work, size_t work_bytes, void* stream);
 
+/* HOST function, no device work: the merge sweeps of track finding - merge_signals (src/identify_tracks.py:725-792)
+ * repeated until a sweep merges nothing, as get_tracks_from_signals does before its length filter (:800-802).
+ * boxes[n][6] = start, end, freq_start, freq_end, mel_freq_start, mel_freq_end of the candidate signals (float64,
+ * the values the reference's Signal objects hold).  A merged box is the bounding box of what it absorbed, so the
+ * result names, per surviving signal and in the reference's final order, which INPUT signals supply its fields:
+ * out[j][5] = {the survivor's own index, index whose start it has, ... whose end, ... freq_start, ... freq_end}
+ * (n rows are written: the *n_out survivors first, then the absorbed signals with the fields they had when they were
+ * absorbed - the reference mutates those objects too).  The caller copies the original objects (ints stay ints).  Same IEEE double
+ * operations in the same order as the reference's Python (tracks.py:_should_merge is the readable restatement and
+ * the test's checker). */
+int cac_tracks_merge(const double* boxes, int32_t n, int32_t* out, int32_t* n_out);
+
 /* The stages after the STFT (:658-686) on a spectrogram the caller supplies: d_spec [rows][cols] = spectogram / a_max.
  * Same kernels as cac_sn_run behind the column medians (taken through a transpose here).  d_result as above for one
  * recording; d_stage_masks (may be NULL) receives the three uint8 [rows][cols] masks (threshold, opened, closed).

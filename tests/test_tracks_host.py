@@ -30,6 +30,43 @@ def test_get_tracks_from_signals_equals_reference(case):
     assert [[t.start, t.end, t.freq_start, t.freq_end] for t in got] == case["tracks"]
 
 
+def _python_sweeps(signals):
+    merged = True
+    while merged:
+        signals, merged = TR.merge_signals(signals)
+    return signals
+
+
+def _boxes(rng, n, quantised):
+    out = []
+    for _ in range(n):
+        t0 = rng.uniform(0, 30)
+        f0 = rng.uniform(0, 9000)
+        box = [t0, t0 + rng.exponential(1.5), f0, f0 + rng.uniform(0, 5000)]
+        if quantised:                                  # many exact ties in every field; ints where the reference has ints
+            box = [round(box[0] * 2) / 2, round(box[1] * 2) / 2 + 0.5, int(box[2] // 500 * 500), int(box[3] // 500 * 500 + 500)]
+        out.append(box)
+    return out
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_native_merge_sweeps_equal_the_python_loop(seed):
+    """cac_tracks_merge (the path get_tracks_from_signals takes) against merge_signals repeated in Python: the same
+    survivors in the same order, every field the same VALUE and the same TYPE, and the absorbed objects left in the
+    state they had when they were absorbed."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(0, 60)) if seed else 0
+    boxes = _boxes(rng, n, quantised=seed % 2 == 1)
+    a, b = [TR.Signal(*x) for x in boxes], [TR.Signal(*x) for x in boxes]
+    want, got = _python_sweeps(a), TR.merge_until_stable(b)
+    key = lambda s: (s.start, s.end, s.freq_start, s.freq_end, s.mel_freq_start, s.mel_freq_end)
+    assert [key(s) for s in got] == [key(s) for s in want]
+    assert [[type(v) for v in key(s)] for s in got] == [[type(v) for v in key(s)] for s in want]
+    assert [b.index(s) for s in got] == [a.index(s) for s in want]                # the same objects survive
+    assert [key(s) for s in b] == [key(s) for s in a]                            # absorbed signals: as they were then
+
+
 def _tracks(case):
     out = []
     for box, tag in zip(case["tracks"], case["tags"]):

@@ -15,3 +15,7 @@ for ch in (64, 32, 24, 16, 12, 8):
         t0 = time.perf_counter(); np.random.seed(1); T.classify_prep_batch(recs, 48000, 3.0, 1.5, chunk=ch, **S1); torch.cuda.synchronize()
         best = min(best, (time.perf_counter() - t0) * 1e3)
     print("chunk %d: %.1f ms for 256 recordings" % (ch, best))
+pr = cProfile.Profile()
+np.random.seed(1)
+pr.enable(); T.classify_prep_batch(recs, 48000, 3.0, 1.5, **S1); torch.cuda.synchronize(); pr.disable()
+st = io.StringIO(); pstats.Stats(pr, stream=st).sort_stats("cumulative").print_stats(28); print(st.getvalue()[:6000])
