@@ -177,6 +177,7 @@ struct RowSelV {
     unsigned mn;
     int mx;
     unsigned below, ncand, v1, v2, min_gt;
+    float tr;
     unsigned sample[32];
     unsigned cand[1024];
 };
@@ -278,8 +279,8 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
     }
     const int nv = cols / (4 * NT);                         // vector slots that are inside the row for every thread
     bool have = nv >= 1;                                    // uniform
-    if (have && tid % (NT / 32) == 0) {                     // sample i: column 4 tid + 4 NT (i mod nv)
-        const int i = tid / (NT / 32), vs = i % nv;
+    if (have && tid % (NT / 32) == 0) {                     // sample i: column 4 tid + 4 NT (i nv / 32)
+        const int i = tid / (NT / 32), vs = (i * nv) >> 5;   // 0 .. nv - 1, spread over the sample
         unsigned sv = key[0];
 #pragma unroll
         for (int v = 1; v < V; ++v)
@@ -386,10 +387,15 @@ __global__ void __launch_bounds__(NT, MINB) sn_rowmed_mask_vec_kernel(const SnWa
         }
         break;
     }
-    const float a = __uint_as_float(w.amax[item]);
-    float med = __fdiv_rn(__uint_as_float(v1), a);
-    if (even) med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);   // np.mean of the two middle values
-    const float tr = unscaled_threshold(__fmul_rn(3.0f, med), a);
+    if (tid < 32) {                                         // one warp turns the order statistics into the row's threshold
+        const float a = __uint_as_float(w.amax[item]);      // (divisions and a walk to the rounding boundary: ~100
+        float med = __fdiv_rn(__uint_as_float(v1), a);      // instructions that 16 warps would each repeat)
+        if (even) med = __fdiv_rn(__fadd_rn(med, __fdiv_rn(__uint_as_float(v2), a)), 2.0f);   // np.mean of the two middle values
+        const float t = unscaled_threshold(__fmul_rn(3.0f, med), a);
+        if (lane == 0) s.tr = t;
+    }
+    __syncthreads();
+    const float tr = s.tr;
     const float* thr = w.colthr + (size_t)item * w.col_stride;
     unsigned* bits = w.bits + (size_t)item * w.bits_stride + (size_t)row * im.wpr;
     const int sh = 4 * (lane & 7);

@@ -46,38 +46,56 @@ __global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWav
     const int bit0 = 32 * w - k / 2;                       // may be negative: arithmetic shift = floor division
     const int i0 = bit0 >> 5;
     const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, wv.rows);
-    for (int r = r_begin; r < r_end; ++r) {
-        const unsigned* row = in + (size_t)r * wpr;
-        unsigned acc = 0u;
-        if (k <= 64) {
-            // the windows all lie inside words i .. i + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
-            // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k
+    if (k <= 64) {
+        // the windows all lie inside words i0 .. i0 + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
+        // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k.
+        // Which of the four words exist, and which of their pixels, depends on the column only: once per thread.
+        bool ok[4];
+        unsigned keep[4];                                  // erosion: the pixels of the complement that exist
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            ok[j] = i0 + j >= 0 && i0 + j < wpr;
+            keep[j] = ok[j] ? valid_bits(i0 + j, cols) : 0u;
+        }
+        int m_top = 1;
+        while (2 * m_top <= k) m_top <<= 1;
+        const int rest = k - m_top, sh = bit0 & 31;        // rest < m_top <= 32
+        const unsigned* row = in + (size_t)r_begin * wpr + i0;
+        unsigned* orow = out + (size_t)r_begin * wpr + w;
+        for (int r = r_begin; r < r_end; ++r, row += wpr, orow += wpr) {
             unsigned A[5];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) A[j] = morph_word<IS_MAX>(row, i0 + j, wpr, cols);
+            for (int j = 0; j < 4; ++j) {
+                const unsigned v = ok[j] ? __ldg(row + j) : 0u;
+                A[j] = IS_MAX ? v : (~v & keep[j]);
+            }
             A[4] = 0u;
-            int m = 1;
-            for (; 2 * m <= k; m <<= 1) {
+            for (int m = 1; m < m_top; m <<= 1) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
             }
-            const int rest = k - m;                        // < m <= 32
             if (rest) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
             }
-            acc = __funnelshift_rc(A[0], A[1], bit0 & 31);
-        } else {
-            int bit = bit0, i = i0;
-            unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
-            for (int d = 0; d < k; ++d, ++bit) {
-                if ((bit >> 5) != i) {
-                    i = bit >> 5;
-                    lo = hi;
-                    hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
-                }
-                acc |= __funnelshift_r(lo, hi, bit & 31);
+            unsigned acc = __funnelshift_rc(A[0], A[1], sh);
+            if (!IS_MAX) acc = ~acc;
+            *orow = acc & vb;
+        }
+        return;
+    }
+    for (int r = r_begin; r < r_end; ++r) {
+        const unsigned* row = in + (size_t)r * wpr;
+        unsigned acc = 0u;
+        int bit = bit0, i = i0;
+        unsigned lo = morph_word<IS_MAX>(row, i, wpr, cols), hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
+        for (int d = 0; d < k; ++d, ++bit) {
+            if ((bit >> 5) != i) {
+                i = bit >> 5;
+                lo = hi;
+                hi = morph_word<IS_MAX>(row, i + 1, wpr, cols);
             }
+            acc |= __funnelshift_r(lo, hi, bit & 31);
         }
         if (!IS_MAX) acc = ~acc;
         out[(size_t)r * wpr + w] = acc & vb;
@@ -85,23 +103,45 @@ __global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWav
 }
 
 // ---- k x 1 rectangle: OR | AND over the rows r - k/2 .. r - k/2 + k - 1 that exist --------------------
-template <bool IS_MAX>
+// KH > 0: the height is a compile-time constant - the strip's 7 + KH input rows are loaded ONCE into registers and
+// every output is a fixed combination of them (the heights of the chain at its native rates: 1, 2, 3, 4, 6, 10);
+// KH = 0: any height, one loop over the rows per output.
+template <bool IS_MAX, int KH>
 __global__ void __launch_bounds__(kMorphThreads) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
     const int wpr = wv.items[blockIdx.z].wpr;
     const int rows = wv.rows;
     const int w = blockIdx.x * kMorphThreads + threadIdx.x;
     if (w >= wpr) return;
+    const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, rows);
     const unsigned* in = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)src_plane * wv.plane_stride + w;
     unsigned* out = wv.bits + (size_t)blockIdx.z * wv.bits_stride + (size_t)dst_plane * wv.plane_stride + w;
-    const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, rows);
-    for (int r = r_begin; r < r_end; ++r) {
-        const int r0 = max(r - k / 2, 0), r1 = min(r - k / 2 + k - 1, rows - 1);
-        unsigned acc = IS_MAX ? 0u : 0xffffffffu;    // AND of real rows keeps the (zero) padding bits zero
-        for (int rr = r0; rr <= r1; ++rr) {
-            const unsigned v = __ldg(in + (size_t)rr * wpr);
-            acc = IS_MAX ? (acc | v) : (acc & v);
+    constexpr unsigned kIdentity = IS_MAX ? 0u : 0xffffffffu;   // AND of real rows keeps the (zero) padding bits zero
+    if constexpr (KH > 0) {
+        constexpr int NIN = kMorphStrip + KH - 1;
+        unsigned L[NIN];
+        const int first = r_begin - KH / 2;
+#pragma unroll
+        for (int t = 0; t < NIN; ++t) {
+            const int rr = first + t;
+            L[t] = (rr >= 0 && rr < rows) ? __ldg(in + (unsigned)(rr * wpr)) : kIdentity;
         }
-        out[(size_t)r * wpr] = acc;
+#pragma unroll
+        for (int j = 0; j < kMorphStrip; ++j) {
+            unsigned acc = L[j];
+#pragma unroll
+            for (int d = 1; d < KH; ++d) acc = IS_MAX ? (acc | L[j + d]) : (acc & L[j + d]);
+            if (r_begin + j < r_end) out[(unsigned)((r_begin + j) * wpr)] = acc;
+        }
+    } else {
+        for (int r = r_begin; r < r_end; ++r) {
+            const int r0 = max(r - k / 2, 0), r1 = min(r - k / 2 + k - 1, rows - 1);
+            unsigned acc = kIdentity;
+            for (int rr = r0; rr <= r1; ++rr) {
+                const unsigned v = __ldg(in + (size_t)rr * wpr);
+                acc = IS_MAX ? (acc | v) : (acc & v);
+            }
+            out[(size_t)r * wpr] = acc;
+        }
     }
 }
 
@@ -295,13 +335,23 @@ cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp
     // (rows ride on grid.y here and in the component kernels: matrices of up to 65,535 rows)
     dim3 grid((unsigned)((max_wpr + kMorphThreads - 1) / kMorphThreads), (unsigned)((w.rows + kMorphStrip - 1) / kMorphStrip),
               (unsigned)w.n_items);
-    if (is_max) {
-        morph_h_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);
-    } else {
-        morph_h_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
-        morph_v_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);
+    if (is_max) morph_h_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
+    else morph_h_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
+#define CAC_MORPH_V(KH)                                                                                         \
+    do {                                                                                                        \
+        if (is_max) morph_v_bits_kernel<true, KH><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh); \
+        else morph_v_bits_kernel<false, KH><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);       \
+    } while (0)
+    switch (kh) {
+        case 1: CAC_MORPH_V(1); break;
+        case 2: CAC_MORPH_V(2); break;
+        case 3: CAC_MORPH_V(3); break;
+        case 4: CAC_MORPH_V(4); break;
+        case 6: CAC_MORPH_V(6); break;
+        case 10: CAC_MORPH_V(10); break;
+        default: CAC_MORPH_V(0); break;
     }
+#undef CAC_MORPH_V
     return cudaGetLastError();
 }
 
