@@ -308,12 +308,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 1) sn_stft_kernel(const flo
                     const int sub = tid / 3, q = tid - 3 * sub;
                     const float* t = tile + (4 * q) * kExFloats;
                     float* o = spec + (size_t)sub * im.pitch + (f0 + r0) + 4 * q;
-#ifdef CAC_SN_FLUSH_UNROLL
-                    constexpr int kFlushUnroll = CAC_SN_FLUSH_UNROLL;
-#else
-                    constexpr int kFlushUnroll = 1;
-#endif
-#pragma unroll kFlushUnroll
                     for (int bin = sub; bin < kSnRows; bin += kRowsPerIt, o += (size_t)kRowsPerIt * im.pitch)
                         *reinterpret_cast<float4*>(o) = make_float4(0.5f * t[bin], 0.5f * t[kExFloats + bin],
                                                                     0.5f * t[2 * kExFloats + bin], 0.5f * t[3 * kExFloats + bin]);

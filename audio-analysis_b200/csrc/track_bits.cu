@@ -47,13 +47,14 @@ __global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWav
     const int i0 = bit0 >> 5;
     const int r_begin = blockIdx.y * kMorphStrip, r_end = min(r_begin + kMorphStrip, wv.rows);
     if (k <= 64) {
-        // the windows all lie inside words i0 .. i0 + 3: OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
-        // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~50 operations instead of 6 per pixel of k.
-        // Which of the four words exist, and which of their pixels, depends on the column only: once per thread.
-        bool ok[4];
-        unsigned keep[4];                                  // erosion: the pixels of the complement that exist
+        // the 32 + k - 1 pixels an output word depends on lie inside words i0 .. i0 + 2 (bit0 mod 32 + k <= 64 for every
+        // k <= 64 with the anchor k / 2): OR of shifts 0 .. m - 1 by doubling (1, 2, 4, ... ), then
+        // [0, k) = [0, m) u [k - m, k) for the largest power of two m <= k: ~40 operations instead of 6 per pixel of k.
+        // Which of the three words exist, and which of their pixels, depends on the column only: once per thread.
+        bool ok[3];
+        unsigned keep[3];                                  // erosion: the pixels of the complement that exist
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 3; ++j) {
             ok[j] = i0 + j >= 0 && i0 + j < wpr;
             keep[j] = ok[j] ? valid_bits(i0 + j, cols) : 0u;
         }
@@ -63,20 +64,20 @@ __global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWav
         const unsigned* row = in + (size_t)r_begin * wpr + i0;
         unsigned* orow = out + (size_t)r_begin * wpr + w;
         for (int r = r_begin; r < r_end; ++r, row += wpr, orow += wpr) {
-            unsigned A[5];
+            unsigned A[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < 3; ++j) {
                 const unsigned v = ok[j] ? __ldg(row + j) : 0u;
                 A[j] = IS_MAX ? v : (~v & keep[j]);
             }
-            A[4] = 0u;
+            A[3] = 0u;
             for (int m = 1; m < m_top; m <<= 1) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
+                for (int j = 0; j < 3; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], m);
             }
             if (rest) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
+                for (int j = 0; j < 3; ++j) A[j] |= __funnelshift_rc(A[j], A[j + 1], rest);
             }
             unsigned acc = __funnelshift_rc(A[0], A[1], sh);
             if (!IS_MAX) acc = ~acc;

@@ -81,7 +81,8 @@ def test_row_medians_exact_on_16_byte_aligned_rows(engine, shape):
     assert len(bad) == 0, (shape, bad[:5])
 
 
-@pytest.mark.parametrize("shape,dh,dw,eh", [((60001, 8), 10, 3, 1), ((37, 700), 7, 70, 2), ((300, 33), 1, 1, 0)])
+@pytest.mark.parametrize("shape,dh,dw,eh", [((60001, 8), 10, 3, 1), ((37, 700), 7, 70, 2), ((300, 33), 1, 1, 0),
+                                               ((50, 300), 3, 64, 1), ((50, 300), 2, 63, 2), ((40, 200), 6, 33, 3)])
 def test_morphology_on_other_shapes_follows_cv2(engine, shape, dh, dw, eh):
     """The strip kernels on matrices unlike the fused chain's: 60,001 rows (a last strip of one row), a structuring
     element wider than 64 pixels, rows shorter than two words, erode height 0 (3 x 3)."""
