@@ -432,15 +432,50 @@ band_gemm_kernel(const __grid_constant__ CUtensorMap a_map, const float* __restr
 
 // Frame g of an item = P rows g - 1 (none for the item's first frame) and g: X[k] = P_prev[k] + (-1)^k P_cur[k] for the 62
 // bins kmin - 1 .. kmin + 60, Hann in the frequency domain, magnitude (power 1) or its square (power 2).
-// One thread per (frame, bin); out[g * nbins + b] like spec4800_kernel's frame-major raw output.
-__global__ void __launch_bounds__(256) band_frames_kernel(const float* __restrict__ P, const long long* __restrict__ frame_base,
-                                                          int n_items, long long total_rows, int kmin, int nbins, int power,
-                                                          float* __restrict__ out, float* gmax) {
-    __shared__ float smax[8];
+// Block = 64 bins x 4 frames, thread (b, y) = bin b of frame 4 blockIdx.x + y: no division to find the frame (the first
+// version numbered the cells flat and divided a 64-bit index by nbins in every thread - more instructions than the work);
+// out[g * nbins + b] like spec4800_kernel's frame-major raw output.
+constexpr int kBfFrames = 4;
+
+// prev / cur: the two P rows of the frame (nullptr = no such chunk), already offset to column 2 b
+__device__ __forceinline__ float band_frame_cell(const float* prev, const float* cur, int bin0, int power) {
+    float xr[3], xi[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const float s = ((bin0 + j) & 1) ? -1.f : 1.f;
+        float2 p = make_float2(0.f, 0.f), c = make_float2(0.f, 0.f);
+        if (prev) p = __ldg(reinterpret_cast<const float2*>(prev) + j);
+        if (cur) c = __ldg(reinterpret_cast<const float2*>(cur) + j);
+        xr[j] = fmaf(s, c.x, p.x);
+        xi[j] = fmaf(s, c.y, p.y);
+    }
+    const float wr = 0.5f * xr[1] - 0.25f * (xr[0] + xr[2]);
+    const float wi = 0.5f * xi[1] - 0.25f * (xi[0] + xi[2]);
+    float mag = fmaf(wr, wr, wi * wi);
+    if (power == 1) mag = sqrtf(mag);
+    return mag;
+}
+
+__device__ __forceinline__ void band_frames_max(float mag, float* smax, float* gmax) {   // all threads of the block call
+    const int t = threadIdx.y * 64 + threadIdx.x;
+    float m = warp_max(mag);
+    if ((t & 31) == 0) smax[t >> 5] = m;
+    __syncthreads();
+    if (t == 0) {
+        for (int w = 1; w < 2 * kBfFrames; ++w) m = fmaxf(m, smax[w]);
+        atomicMax(reinterpret_cast<unsigned*>(gmax), __float_as_uint(m));
+    }
+}
+
+__global__ void __launch_bounds__(64 * kBfFrames) band_frames_kernel(const float* __restrict__ P, const long long* __restrict__ frame_base,
+                                                                     int n_items, long long total_rows, int kmin, int nbins, int power,
+                                                                     float* __restrict__ out, float* gmax) {
+    __shared__ float smax[2 * kBfFrames];
     __shared__ int s_lo;
-    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (threadIdx.x == 0) {                    // the item of the block's first frame: one search per block, the threads walk on
-        const long long g0 = ((long long)blockIdx.x * 256) / nbins;
+    const long long g = (long long)blockIdx.x * kBfFrames + threadIdx.y;
+    const int b = threadIdx.x;
+    if (threadIdx.x == 0 && threadIdx.y == 0) {   // the item of the block's first frame: one search per block, the threads walk on
+        const long long g0 = (long long)blockIdx.x * kBfFrames;
         int lo = 0, hi = n_items - 1;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
@@ -450,79 +485,41 @@ __global__ void __launch_bounds__(256) band_frames_kernel(const float* __restric
     }
     __syncthreads();
     float mag = 0.f;
-    if (idx < total_rows * nbins) {
-        const long long g = idx / nbins;
-        const int b = (int)(idx - g * nbins);
+    if (g < total_rows && b < nbins) {
         int lo = s_lo;
         while (frame_base[lo + 1] <= g) ++lo;                          // g < total_rows = frame_base[n_items]
-        const bool first = frame_base[lo] == g;
         const float* cur = P + (size_t)g * kBgN + 2 * b;               // columns 2 j, 2 j + 1 = bin kmin - 1 + j; j = b, b + 1, b + 2
-        float xr[3], xi[3];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const float s = ((kmin - 1 + b + j) & 1) ? -1.f : 1.f;
-            float pr = 0.f, pi = 0.f;
-            if (!first) { pr = cur[2 * j - kBgN]; pi = cur[2 * j + 1 - kBgN]; }
-            xr[j] = fmaf(s, cur[2 * j], pr);
-            xi[j] = fmaf(s, cur[2 * j + 1], pi);
-        }
-        const float wr = 0.5f * xr[1] - 0.25f * (xr[0] + xr[2]);
-        const float wi = 0.5f * xi[1] - 0.25f * (xi[0] + xi[2]);
-        mag = fmaf(wr, wr, wi * wi);
-        if (power == 1) mag = sqrtf(mag);
-        out[idx] = mag;
+        mag = band_frame_cell(frame_base[lo] == g ? nullptr : cur - kBgN, cur, kmin - 1 + b, power);
+        out[g * nbins + b] = mag;
     }
-    if (gmax) {
-        float m = warp_max(mag);
-        if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            for (int w = 1; w < 8; ++w) m = fmaxf(m, smax[w]);
-            atomicMax(reinterpret_cast<unsigned*>(gmax), __float_as_uint(m));
-        }
-    }
+    if (gmax) band_frames_max(mag, smax, gmax);
 }
 
 // The same for the TMA form's row numbering: item i owns the chunk rows [i C, i C + C) of P and the frames [i (C + 1),
 // (i + 1) (C + 1)); frame f = chunk f - 1 (none for f = 0) followed by chunk f (all zeros for f = C: centre padding).
-__global__ void __launch_bounds__(256) band_frames_uniform_kernel(const float* __restrict__ P, int chunks_per_item,
-                                                                  long long total_frames, int kmin, int nbins, int power,
-                                                                  float* __restrict__ out, float* gmax) {
-    __shared__ float smax[8];
-    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+__global__ void __launch_bounds__(64 * kBfFrames) band_frames_uniform_kernel(const float* __restrict__ P, int chunks_per_item,
+                                                                             long long total_frames, int kmin, int nbins, int power,
+                                                                             float* __restrict__ out, float* gmax) {
+    __shared__ float smax[2 * kBfFrames];
+    const long long g = (long long)blockIdx.x * kBfFrames + threadIdx.y;
+    const int b = threadIdx.x;
     float mag = 0.f;
-    if (idx < total_frames * nbins) {
-        const long long g = idx / nbins;
-        const int b = (int)(idx - g * nbins);
-        const long long item = g / (chunks_per_item + 1);
-        const int f = (int)(g - item * (chunks_per_item + 1));
+    if (g < total_frames && b < nbins) {
+        long long item;
+        int f;
+        if (total_frames <= 0x7fffffffLL) {                            // the usual case: 32-bit division
+            const unsigned gi = (unsigned)g, per = (unsigned)(chunks_per_item + 1);
+            item = gi / per;
+            f = (int)(gi - (unsigned)item * per);
+        } else {
+            item = g / (chunks_per_item + 1);
+            f = (int)(g - item * (chunks_per_item + 1));
+        }
         const float* cur = P + (size_t)(item * chunks_per_item + f) * kBgN + 2 * b;
-        const bool has_prev = f > 0, has_cur = f < chunks_per_item;
-        float xr[3], xi[3];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const float s = ((kmin - 1 + b + j) & 1) ? -1.f : 1.f;
-            float pr = 0.f, pi = 0.f, cr = 0.f, ci = 0.f;
-            if (has_prev) { pr = cur[2 * j - kBgN]; pi = cur[2 * j + 1 - kBgN]; }
-            if (has_cur) { cr = cur[2 * j]; ci = cur[2 * j + 1]; }
-            xr[j] = fmaf(s, cr, pr);
-            xi[j] = fmaf(s, ci, pi);
-        }
-        const float wr = 0.5f * xr[1] - 0.25f * (xr[0] + xr[2]);
-        const float wi = 0.5f * xi[1] - 0.25f * (xi[0] + xi[2]);
-        mag = fmaf(wr, wr, wi * wi);
-        if (power == 1) mag = sqrtf(mag);
-        out[idx] = mag;
+        mag = band_frame_cell(f > 0 ? cur - kBgN : nullptr, f < chunks_per_item ? cur : nullptr, kmin - 1 + b, power);
+        out[g * nbins + b] = mag;
     }
-    if (gmax) {
-        float m = warp_max(mag);
-        if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            for (int w = 1; w < 8; ++w) m = fmaxf(m, smax[w]);
-            atomicMax(reinterpret_cast<unsigned*>(gmax), __float_as_uint(m));
-        }
-    }
+    if (gmax) band_frames_max(mag, smax, gmax);
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
@@ -617,9 +614,8 @@ cudaError_t launch_band_gemm(const SpecArgs& a, const float* base, int uniform_c
         const long long tiles = (rows + kBgM - 1) / kBgM;
         band_gemm_kernel<true><<<(unsigned)(tiles < sms ? tiles : sms), kBgThreads, kBgSmemBytes, st>>>(
             a_map, nullptr, nullptr, nullptr, nullptr, 0, rows, a.hop, d_bsw, d_P);
-        const long long cells = frames * a.nbins;
-        band_frames_uniform_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(d_P, uniform_chunks, frames, a.kmin, a.nbins,
-                                                                                    a.power, a.out, a.gmax);
+        band_frames_uniform_kernel<<<(unsigned)((frames + kBfFrames - 1) / kBfFrames), dim3(64, kBfFrames), 0, st>>>(
+            d_P, uniform_chunks, frames, a.kmin, a.nbins, a.power, a.out, a.gmax);
         return cudaGetLastError();
     }
     const long long rows = a.n_frames_total;
@@ -629,9 +625,8 @@ cudaError_t launch_band_gemm(const SpecArgs& a, const float* base, int uniform_c
     const long long tiles = (rows + kBgM - 1) / kBgM;
     band_gemm_kernel<false><<<(unsigned)(tiles < sms ? tiles : sms), kBgThreads, kBgSmemBytes, st>>>(
         a_map, a.pcm, a.item_off, a.item_len, a.frame_base, a.n_items, rows, a.hop, d_bsw, d_P);
-    const long long cells = rows * a.nbins;
-    band_frames_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(d_P, a.frame_base, a.n_items, rows, a.kmin, a.nbins,
-                                                                        a.power, a.out, a.gmax);
+    band_frames_kernel<<<(unsigned)((rows + kBfFrames - 1) / kBfFrames), dim3(64, kBfFrames), 0, st>>>(
+        d_P, a.frame_base, a.n_items, rows, a.kmin, a.nbins, a.power, a.out, a.gmax);
     return cudaGetLastError();
 }
 
