@@ -150,7 +150,7 @@ def path_pipeline(n_rec=256, cpu=True):
     ge_ms = timed(lambda: ge.get_end_chunks(flat, tabs[0], tabs[1], 48000 // 281, max_item_samples=n), steps=5)
     sn_ms = timed(lambda: sn.run(flat, tabs[0], tabs[1], max_components=4096, max_item_samples=n), steps=5)
     np.random.seed(0)
-    total_ms, res = wall(lambda: T.classify_prep_batch(pcm, 48000, 3.0, 1.5, **S1), warmup=1, steps=2)
+    total_ms, res = wall(lambda: T.classify_prep_batch(pcm, 48000, 3.0, 1.5, **S1), warmup=2, steps=4)
     n_tracks = sum(len(r["tracks"]) for r in res)
     n_segs = sum(int(s.shape[0]) for r in res if r["samples"] for s in r["samples"])
     out_bytes = n_segs * 160 * 513 * 4
