@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(kMorphThreads) morph_h_bits_kernel(const SnWav
 
 // ---- k x 1 rectangle: OR | AND over the rows r - k/2 .. r - k/2 + k - 1 that exist --------------------
 // KH > 0: the height is a compile-time constant - the strip's 7 + KH input rows are loaded ONCE into registers and
-// every output is a fixed combination of them (the heights of the chain at its native rates: 1, 2, 3, 4, 6, 10);
+// every output is a fixed combination of them (the heights of the chain at its native rates: 2, 3, 4, 6, 10; a height of 1 skips this pass);
 // KH = 0: any height, one loop over the rows per output.
 template <bool IS_MAX, int KH>
 __global__ void __launch_bounds__(kMorphThreads) morph_v_bits_kernel(const SnWave wv, int src_plane, int dst_plane, int k) {
@@ -336,15 +336,16 @@ cudaError_t launch_morph_rect_bits_batch(const SnWave& w, int src_plane, int tmp
     // (rows ride on grid.y here and in the component kernels: matrices of up to 65,535 rows)
     dim3 grid((unsigned)((max_wpr + kMorphThreads - 1) / kMorphThreads), (unsigned)((w.rows + kMorphStrip - 1) / kMorphStrip),
               (unsigned)w.n_items);
-    if (is_max) morph_h_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
-    else morph_h_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, src_plane, tmp_plane, kw);
+    const int h_dst = kh == 1 ? dst_plane : tmp_plane;     // a height of 1: the horizontal pass is the whole operation
+    if (is_max) morph_h_bits_kernel<true><<<grid, kMorphThreads, 0, st>>>(w, src_plane, h_dst, kw);
+    else morph_h_bits_kernel<false><<<grid, kMorphThreads, 0, st>>>(w, src_plane, h_dst, kw);
+    if (kh == 1) return cudaGetLastError();
 #define CAC_MORPH_V(KH)                                                                                         \
     do {                                                                                                        \
         if (is_max) morph_v_bits_kernel<true, KH><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh); \
         else morph_v_bits_kernel<false, KH><<<grid, kMorphThreads, 0, st>>>(w, tmp_plane, dst_plane, kh);       \
     } while (0)
     switch (kh) {
-        case 1: CAC_MORPH_V(1); break;
         case 2: CAC_MORPH_V(2); break;
         case 3: CAC_MORPH_V(3); break;
         case 4: CAC_MORPH_V(4); break;
