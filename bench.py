@@ -458,6 +458,8 @@ def main():
         if not args.no_e2e:
             out_host_t = out_host = host_in_t = pool_np = host_in16_t = pool_np16 = maxima_host = flat_in = None
         torch.cuda.empty_cache()
+        if numa_cpus:
+            os.sched_setaffinity(0, numa_cpus)             # back next to the GPU: the paths have host halves (track merging)
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import bench_paths
         line["paths"] = {}

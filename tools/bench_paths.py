@@ -149,6 +149,8 @@ def path_pipeline(n_rec=256, cpu=True):
     flat = pcm.view(-1)
     ge_ms = timed(lambda: ge.get_end_chunks(flat, tabs[0], tabs[1], 48000 // 281, max_item_samples=n), steps=5)
     sn_ms = timed(lambda: sn.run(flat, tabs[0], tabs[1], max_components=4096, max_item_samples=n), steps=5)
+    import gc
+    gc.collect()                                           # start the wall-clock region without another path's garbage
     np.random.seed(0)
     total_ms, res = wall(lambda: T.classify_prep_batch(pcm, 48000, 3.0, 1.5, **S1), warmup=2, steps=4)
     n_tracks = sum(len(r["tracks"]) for r in res)
